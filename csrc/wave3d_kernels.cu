@@ -1,0 +1,905 @@
+// wave3d_kernels.cu — sm_100a device code of the wave3d solver.
+//
+// Hot kernel: k_step<RJ,FIRST,DIV> — one launch per time layer that fuses what the
+// reference spreads over K2/K3 (update), K4 (boundary planes), K5/K6 + 12 memcpys +
+// MPI p2p (halo exchange), K7 + host loop (error max) and two memsets
+// (ref: cuda_sol.cpp:384-421, cuda_sol_kernels.cu:24-268).
+//
+// Design (B200-first, not a translation):
+//   * The stencil source layer u^{n-1} and the in-place layer u^{n-2} stream through
+//     shared memory as y-z tiles, one x plane at a time, moved by TMA bulk tensor
+//     loads (cp.async.bulk.tensor.3d -> UTMALDG) into mbarrier-guarded rings; threads
+//     never issue a global load on the hot path.
+//   * Each thread owns 2 z-cells x RJ rows, reads its 7-point neighbourhood from the
+//     three resident planes and writes u^n with one 16-byte store over u^{n-2}.
+//   * The analytic solution is separable: f = ((c*sx[i])*sy[j])*sz[k] with 1-D sine
+//     tables -> bit-identical to the reference's per-cell trig at 3 multiplies.
+//     max|u-f| is an in-register max; max|u-f|/|f| uses a monotone filter so the
+//     exact IEEE division runs only for candidates of the maximum.
+//   * Face cells are stored a second time, straight into the neighbour GPU's ghost
+//     cells (peer-mapped memory over NVLink; own memory for the periodic self-wrap).
+//     The last CTA of the grid publishes an epoch flag per neighbour with
+//     st.release.sys; the next step's CTAs ld.acquire.sys-spin on their inbound flags.
+//     No pack/unpack kernels, no host staging, no MPI/NCCL on this path.
+//   * Per-layer maxima land in err[2n..2n+1] via atomicMax on the u64 bit pattern
+//     (values are >= 0; NaN never wins, like fmax) and are forwarded to rank 0's
+//     table with a system-scope atomic (the reference's deferred MPI_Reduce).
+#include "wave3d_internal.hpp"
+
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+
+namespace w3d {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& s) { g_last_error = s; }
+bool check(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
+    return false;
+}
+
+// ----------------------------------------------------------------- PTX helpers
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// ------------------------------------------------------------- step parameters
+
+struct alignas(64) StepParams {
+    CUtensorMap map_src;
+    CUtensorMap map_io;
+    double* out;
+    const double* sx;
+    const double* sy;
+    const double* sz;
+    const double* rsx;
+    const double* rsy;
+    const double* rsz;
+    double* dst[6];
+    int64_t sa[6];
+    int64_t sb[6];
+    uint32_t* flag_out[6];
+    const uint32_t* flag_in[6];
+    uint64_t* err;       // &table[2n]
+    uint64_t* root_err;  // &root_table[2n] or nullptr
+    uint32_t* scratch;
+    const double* desc;  // optional uploaded step descriptor {arg_t, coef}
+    int64_t ps, pitch;
+    double coef, arg_t;
+    double hx2, hy2, hz2, rx, ry, rz;
+    unsigned long long timeout_ns;
+    int oz, X, Y, Z;
+    int lo1, hi1, lo2, hi2;
+    int elo0, ehi0;
+    int nty, ntz, nchunks, ty, tz;
+    int s1, s0;
+    int send_x0, send_x1;
+    uint32_t epoch_wait, epoch_pub;
+    uint32_t push_mask;  // bit f set: dst[f] != nullptr
+};
+
+// Division of a stencil sum by the constant d = h^2 with r = rn(1/d).
+template <int DIV>
+__device__ __forceinline__ double div_const(double x, double d, double r) {
+    if (DIV == 0) {
+        return __dmul_rn(x, r);  // d is a power of two: exact
+    } else if (DIV == 1) {
+        double q = __dmul_rn(x, r);
+        double e = __fma_rn(-d, q, x);
+        return __fma_rn(e, r, q);
+    } else if (DIV == 2) {
+        // Markstein: q1 is faithful after one correction; with r = RN(1/d) a second
+        // exact-remainder correction of a faithful quotient is correctly rounded.
+        double q = __dmul_rn(x, r);
+        double e = __fma_rn(-d, q, x);
+        q = __fma_rn(e, r, q);
+        e = __fma_rn(-d, q, x);
+        return __fma_rn(e, r, q);
+    } else {
+        return __ddiv_rn(x, d);
+    }
+}
+
+struct ErrAcc {
+    double mabs, mrel, best, thr;
+};
+
+// Error bookkeeping for one cell. cand approximates a/|f| to ~1e-15 relative via
+// reciprocal tables; the exact division runs only if cand can still be the maximum
+// (band 2^-40 >> table error), so the result equals max over all cells of the
+// reference's `abs_error / fabs(f)` (ref: cuda_sol_kernels.cu:42-45).
+__device__ __forceinline__ void err_cell(ErrAcc& e, double u, double f, double rxy, double rszk) {
+    const double a = fabs(__dsub_rn(u, f));
+    e.mabs = fmax(e.mabs, a);
+    const double cand = __dmul_rn(__dmul_rn(a, rxy), rszk);
+    if (cand >= e.thr) {
+        e.mrel = fmax(e.mrel, __ddiv_rn(a, fabs(f)));
+        e.best = fmax(e.best, cand);
+        e.thr = e.best * (1.0 - 0x1p-40);
+    }
+}
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ void store_pair(double* p, double a, double b, bool v0, bool v1) {
+    if (v1 && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+        *reinterpret_cast<double2*>(p) = make_double2(a, b);
+    } else {
+        if (v0) p[0] = a;
+        if (v1) p[1] = b;
+    }
+}
+
+constexpr int kMaxWarps = 16;
+
+template <int RJ, bool FIRST, int DIV>
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) k_step(const __grid_constant__ StepParams p) {
+    extern __shared__ unsigned char smem_raw[];
+    __shared__ double s_bcast[3];
+    __shared__ double s_red[kMaxWarps][2];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W1 = p.tz + 4;                                     // halo slot row length (doubles)
+    const uint32_t slot1_bytes = (uint32_t)(((p.ty + 2) * W1 * 8 + 127) & ~127);
+    const uint32_t slot0_bytes = (uint32_t)((p.ty * p.tz * 8 + 127) & ~127);
+    const uint32_t box1_bytes = (uint32_t)((p.ty + 2) * W1 * 8);
+    const uint32_t box0_bytes = (uint32_t)(p.ty * p.tz * 8);
+
+    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    unsigned char* ring1 = base;
+    unsigned char* ring0 = ring1 + (size_t)p.s1 * slot1_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ring0 + (size_t)(FIRST ? 0 : p.s0) * slot0_bytes);
+    const uint32_t bar1 = smem_u32(bars);              // full barriers of ring1
+    const uint32_t bar0 = bar1 + 8u * (uint32_t)p.s1;  // full barriers of ring0
+
+    // ---- work item
+    const int bid = blockIdx.x;
+    const int tzi = bid % p.ntz;
+    const int tyi = (bid / p.ntz) % p.nty;
+    const int cxi = bid / (p.ntz * p.nty);
+    const int j0 = p.lo1 + tyi * p.ty;
+    const int k0 = p.lo2 + tzi * p.tz;
+    const int xa = (int)(((int64_t)p.X * cxi) / p.nchunks);
+    const int xb = (int)(((int64_t)p.X * (cxi + 1)) / p.nchunks);
+    const int nplanes = xb - xa;
+
+    // TMA box origins in storage coordinates
+    const int c0_src = p.oz + k0 - 2, c1_src = j0;  // row(j0) - 1 = j0
+    const int c0_io = p.oz + k0, c1_io = j0 + 1;
+
+    if (tid == 0) {
+        // Neighbours must have finished the previous layer: their ghost stores are
+        // complete (RAW) and they no longer read the ghosts we are about to overwrite (WAR).
+        const unsigned long long t0 = globaltimer_ns();
+        for (int f = 0; f < 6; f++) {
+            const uint32_t* fl = p.flag_in[f];
+            if (!fl) continue;
+            while (ld_acquire_sys(fl) < p.epoch_wait) {
+                __nanosleep(64);
+                if (globaltimer_ns() - t0 > p.timeout_ns) {
+                    atomicExch(&p.scratch[1], 1u);
+                    break;
+                }
+            }
+        }
+        asm volatile("fence.proxy.async;" ::: "memory");
+        for (int s = 0; s < p.s1; s++) mbar_init(bar1 + 8u * s, 1);
+        if (!FIRST)
+            for (int s = 0; s < p.s0; s++) mbar_init(bar0 + 8u * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        // prologue loads: source planes xa-1 .. , in-place planes xa ..
+        const int n1 = min(p.s1, nplanes + 2);
+        for (int q = 0; q < n1; q++) {
+            mbar_expect_tx(bar1 + 8u * q, box1_bytes);
+            tma_load_3d(smem_u32(ring1 + (size_t)q * slot1_bytes), &p.map_src, c0_src, c1_src, xa + q, bar1 + 8u * q);
+        }
+        if (!FIRST) {
+            const int n0 = min(p.s0, nplanes);
+            for (int q = 0; q < n0; q++) {
+                mbar_expect_tx(bar0 + 8u * q, box0_bytes);
+                tma_load_3d(smem_u32(ring0 + (size_t)q * slot0_bytes), &p.map_io, c0_io, c1_io, xa + 1 + q, bar0 + 8u * q);
+            }
+        }
+        // the layer's time argument and coefficient come from the launch parameters or,
+        // in per-step (end-to-end) mode, from the descriptor the host uploaded for this step
+        const double arg_t = p.desc ? p.desc[0] : p.arg_t;
+        const double c = cos(arg_t);
+        s_bcast[0] = c;
+        s_bcast[1] = __ddiv_rn(1.0, fabs(c));
+        s_bcast[2] = p.desc ? p.desc[1] : p.coef;
+    }
+    __syncthreads();
+    const double cosn = s_bcast[0];
+    const double rcos = s_bcast[1];
+    const double coef = s_bcast[2];
+
+    // ---- per-thread geometry
+    const int kk = k0 + 2 * lane;  // owned k of the first cell
+    const bool vk0 = kk <= p.hi2, vk1 = kk + 1 <= p.hi2;
+    bool vj[RJ];
+    double syq[RJ], rsyq[RJ];
+#pragma unroll
+    for (int q = 0; q < RJ; q++) {
+        const int j = j0 + warp * RJ + q;
+        vj[q] = j <= p.hi1;
+        syq[q] = vj[q] ? p.sy[j] : 0.0;
+        rsyq[q] = vj[q] ? p.rsy[j] : 0.0;
+    }
+    const double szk0 = vk0 ? p.sz[kk] : 0.0, szk1 = vk1 ? p.sz[kk + 1] : 0.0;
+    const double rsz0 = vk0 ? p.rsz[kk] : 0.0, rsz1 = vk1 ? p.rsz[kk + 1] : 0.0;
+    const bool zlo_face = (p.push_mask & 16u) && kk == 0;  // owned k == 0 is cell .x of lane 0 of z-tile 0
+    const bool zhi_face0 = (p.push_mask & 32u) && kk == p.Z - 1;
+    const bool zhi_face1 = (p.push_mask & 32u) && kk + 1 == p.Z - 1;
+
+    ErrAcc ea = {0.0, 0.0, 0.0, 0.0};
+
+    const int colc = 2 + 2 * lane;  // my first cell inside a halo-slot row
+    mbar_wait(bar1, 0);
+    if (p.s1 > 1) mbar_wait(bar1 + 8u, 0);
+
+    for (int t = 0; t < nplanes; t++) {
+        const int i = xa + t;  // owned x index of the centre plane
+        {
+            const int q = t + 2;
+            mbar_wait(bar1 + 8u * (q % p.s1), (uint32_t)((q / p.s1) & 1));
+        }
+        if (!FIRST) mbar_wait(bar0 + 8u * (t % p.s0), (uint32_t)((t / p.s0) & 1));
+
+        const double* sm = reinterpret_cast<const double*>(ring1 + (size_t)(t % p.s1) * slot1_bytes);
+        const double* sc = reinterpret_cast<const double*>(ring1 + (size_t)((t + 1) % p.s1) * slot1_bytes);
+        const double* sp = reinterpret_cast<const double*>(ring1 + (size_t)((t + 2) % p.s1) * slot1_bytes);
+        const double* s0 = reinterpret_cast<const double*>(ring0 + (size_t)(FIRST ? 0 : (t % p.s0)) * slot0_bytes);
+
+        const bool ei = i >= p.elo0 && i <= p.ehi0;
+        const double cs = __dmul_rn(cosn, p.sx[i]);
+        const double rcs = __dmul_rn(rcos, p.rsx[i]);
+        const bool xlo_face = (p.push_mask & 1u) && i == p.send_x0;
+        const bool xhi_face = (p.push_mask & 2u) && i == p.send_x1;
+
+        const int r0 = warp * RJ;
+        double2 rowc[RJ + 2];
+#pragma unroll
+        for (int q = 0; q < RJ + 2; q++) rowc[q] = *reinterpret_cast<const double2*>(sc + (r0 + q) * W1 + colc);
+
+#pragma unroll
+        for (int q = 0; q < RJ; q++) {
+            const int r = r0 + q;
+            const double2 c = rowc[q + 1], ym = rowc[q], yp = rowc[q + 2];
+            const double zl = sc[(r + 1) * W1 + colc - 1];
+            const double zr = sc[(r + 1) * W1 + colc + 2];
+            const double2 xm = *reinterpret_cast<const double2*>(sm + (r + 1) * W1 + colc);
+            const double2 xp = *reinterpret_cast<const double2*>(sp + (r + 1) * W1 + colc);
+            double2 g0 = c;
+            if (!FIRST) g0 = *reinterpret_cast<const double2*>(s0 + r * p.tz + 2 * lane);
+
+            // exact expression order of the reference build
+            const double c2a = __dadd_rn(c.x, c.x), c2b = __dadd_rn(c.y, c.y);
+            const double sa_ = FIRST ? c.x : __dsub_rn(c2a, g0.x);
+            const double sb_ = FIRST ? c.y : __dsub_rn(c2b, g0.y);
+            const double lxa = div_const<DIV>(__dsub_rn(__dadd_rn(xp.x, xm.x), c2a), p.hx2, p.rx);
+            const double lxb = div_const<DIV>(__dsub_rn(__dadd_rn(xp.y, xm.y), c2b), p.hx2, p.rx);
+            const double lya = div_const<DIV>(__dsub_rn(__dadd_rn(yp.x, ym.x), c2a), p.hy2, p.ry);
+            const double lyb = div_const<DIV>(__dsub_rn(__dadd_rn(yp.y, ym.y), c2b), p.hy2, p.ry);
+            const double lza = div_const<DIV>(__dsub_rn(__dadd_rn(c.y, zl), c2a), p.hz2, p.rz);
+            const double lzb = div_const<DIV>(__dsub_rn(__dadd_rn(zr, c.x), c2b), p.hz2, p.rz);
+            const double ua = __fma_rn(coef, __dadd_rn(__dadd_rn(lxa, lya), lza), sa_);
+            const double ub = __fma_rn(coef, __dadd_rn(__dadd_rn(lxb, lyb), lzb), sb_);
+
+            const int j = j0 + r;
+            const bool v0 = vj[q] && vk0, v1 = vj[q] && vk1;
+            if (v0) {
+                double* o = p.out + (int64_t)(i + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
+                store_pair(o, ua, ub, true, v1);
+                if (p.push_mask) {
+                    if (xlo_face) store_pair(p.dst[0] + j * p.sa[0] + kk * p.sb[0], ua, ub, true, v1 && p.sb[0] == 1);
+                    if (xlo_face && v1 && p.sb[0] != 1) p.dst[0][j * p.sa[0] + (kk + 1) * p.sb[0]] = ub;
+                    if (xhi_face) store_pair(p.dst[1] + j * p.sa[1] + kk * p.sb[1], ua, ub, true, v1 && p.sb[1] == 1);
+                    if (xhi_face && v1 && p.sb[1] != 1) p.dst[1][j * p.sa[1] + (kk + 1) * p.sb[1]] = ub;
+                    if ((p.push_mask & 4u) && j == 0) {
+                        store_pair(p.dst[2] + i * p.sa[2] + kk * p.sb[2], ua, ub, true, v1 && p.sb[2] == 1);
+                        if (v1 && p.sb[2] != 1) p.dst[2][i * p.sa[2] + (kk + 1) * p.sb[2]] = ub;
+                    }
+                    if ((p.push_mask & 8u) && j == p.Y - 1) {
+                        store_pair(p.dst[3] + i * p.sa[3] + kk * p.sb[3], ua, ub, true, v1 && p.sb[3] == 1);
+                        if (v1 && p.sb[3] != 1) p.dst[3][i * p.sa[3] + (kk + 1) * p.sb[3]] = ub;
+                    }
+                    if (zlo_face) p.dst[4][i * p.sa[4] + j * p.sb[4]] = ua;
+                    if (zhi_face0) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ua;
+                    if (zhi_face1 && v1) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ub;
+                }
+                if (ei) {
+                    const double fxy = __dmul_rn(cs, syq[q]);
+                    const double rxy = __dmul_rn(rcs, rsyq[q]);
+                    err_cell(ea, ua, __dmul_rn(fxy, szk0), rxy, rsz0);
+                    if (v1) err_cell(ea, ub, __dmul_rn(fxy, szk1), rxy, rsz1);
+                }
+            }
+        }
+
+        __syncthreads();  // everyone is done with plane i-1 (ring1 slot t) and in-place plane i (ring0 slot t)
+        if (tid == 0) {
+            const int q1 = t + p.s1;
+            if (q1 < nplanes + 2) {
+                const uint32_t b = bar1 + 8u * (t % p.s1);
+                mbar_expect_tx(b, box1_bytes);
+                tma_load_3d(smem_u32(ring1 + (size_t)(t % p.s1) * slot1_bytes), &p.map_src, c0_src, c1_src, xa + q1, b);
+            }
+            if (!FIRST) {
+                const int q0 = t + p.s0;
+                if (q0 < nplanes) {
+                    const uint32_t b = bar0 + 8u * (t % p.s0);
+                    mbar_expect_tx(b, box0_bytes);
+                    tma_load_3d(smem_u32(ring0 + (size_t)(t % p.s0) * slot0_bytes), &p.map_io, c0_io, c1_io, xa + 1 + q0, b);
+                }
+            }
+        }
+    }
+
+    // ---- error maxima: warp -> CTA -> device table
+    const double wa = warp_max(ea.mabs), wr = warp_max(ea.mrel);
+    if (lane == 0) {
+        s_red[warp][0] = wa;
+        s_red[warp][1] = wr;
+    }
+    __syncthreads();  // also orders every thread's global / peer stores before thread 0's fence
+    if (tid == 0) {
+        double a = 0.0, r = 0.0;
+        const int nw = blockDim.x >> 5;
+        for (int w = 0; w < nw; w++) {
+            a = fmax(a, s_red[w][0]);
+            r = fmax(r, s_red[w][1]);
+        }
+        if (a > 0.0) atomicMax(reinterpret_cast<unsigned long long*>(p.err), (unsigned long long)__double_as_longlong(a));
+        if (r > 0.0) atomicMax(reinterpret_cast<unsigned long long*>(p.err + 1), (unsigned long long)__double_as_longlong(r));
+        __threadfence_system();
+        const uint32_t ticket = atomicAdd(&p.scratch[0], 1u);
+        if (ticket == gridDim.x - 1) {
+            // last CTA of the layer: every face store of this GPU is ordered before this point
+            __threadfence_system();
+            p.scratch[0] = 0;
+            if (p.root_err) {
+                const unsigned long long va = atomicMax(reinterpret_cast<unsigned long long*>(p.err), 0ull);
+                const unsigned long long vr = atomicMax(reinterpret_cast<unsigned long long*>(p.err + 1), 0ull);
+                atomicMax_system(reinterpret_cast<unsigned long long*>(p.root_err), va);
+                atomicMax_system(reinterpret_cast<unsigned long long*>(p.root_err + 1), vr);
+            }
+            for (int f = 0; f < 6; f++)
+                if (p.flag_out[f]) st_release_sys(p.flag_out[f], p.epoch_pub);
+        }
+    }
+}
+
+// ------------------------------------------------------------- small kernels
+
+struct TabParams {
+    double pi, hx, hy, hz, Lx, Ly, Lz;
+    int n[3], o[3];
+};
+
+// Sine tables with the reference's argument expressions and libdevice sin
+// (ref: cuda_sol_kernels.cu:41,184) plus reciprocals for the rel-error filter.
+__global__ void k_tables(TabParams tp, double* sx, double* sy, double* sz, double* rsx, double* rsy, double* rsz) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int axis = blockIdx.y;
+    if (t >= tp.n[axis]) return;
+    const double g = (double)(t + tp.o[axis]);
+    double arg;
+    if (axis == 0) arg = __ddiv_rn(__dmul_rn(__dmul_rn(__dadd_rn(tp.pi, tp.pi), tp.hx), g), tp.Lx);
+    else if (axis == 1) arg = __ddiv_rn(__dmul_rn(__dmul_rn(tp.pi, tp.hy), g), tp.Ly);
+    else arg = __ddiv_rn(__dmul_rn(__dmul_rn(tp.pi, tp.hz), g), tp.Lz);
+    const double s = sin(arg);
+    const double r = __ddiv_rn(1.0, fabs(s));
+    if (axis == 0) { sx[t] = s; rsx[t] = r; }
+    else if (axis == 1) { sy[t] = s; rsy[t] = r; }
+    else { sz[t] = s; rsz[t] = r; }
+}
+
+__global__ void k_layer0(double* u, const double* sx, const double* sy, const double* sz, double arg_t, int X, int Y,
+                         int Z, int64_t ps, int64_t pitch, int oz) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    if (k >= Z || j >= Y) return;
+    const double c = cos(arg_t);
+    const double syj = sy[j], szk = sz[k];
+    for (int i = blockIdx.z; i < X; i += gridDim.z) {
+        const double f = __dmul_rn(__dmul_rn(__dmul_rn(c, sx[i]), syj), szk);
+        u[(int64_t)(i + 1) * ps + (int64_t)(j + 1) * pitch + (oz + k)] = f;
+    }
+}
+
+__global__ void k_zero_walls(double* u, int X, int Y, int Z, int64_t ps, int64_t pitch, int oz, int mask) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    double* pl = u + (int64_t)(i + 1) * ps;
+    if (t < Z) {
+        if (mask & 1) pl[(int64_t)1 * pitch + oz + t] = 0.0;
+        if (mask & 2) pl[(int64_t)Y * pitch + oz + t] = 0.0;
+    }
+    if (t < Y) {
+        if (mask & 4) pl[(int64_t)(t + 1) * pitch + oz] = 0.0;
+        if (mask & 8) pl[(int64_t)(t + 1) * pitch + oz + Z - 1] = 0.0;
+    }
+}
+
+// face <-> packed buffer / peer ghost copy. mode 0: pack, 1: unpack, 2: push to peer.
+struct FaceParams {
+    int X, Y, Z, oz;
+    int64_t ps, pitch;
+    int send_x0, send_x1;
+};
+__device__ __forceinline__ int64_t sidx(const FaceParams& g, int i, int j, int k) {
+    return (int64_t)(i + 1) * g.ps + (int64_t)(j + 1) * g.pitch + (g.oz + k);
+}
+__global__ void k_face(FaceParams g, double* u, int face, int mode, double* buf, int64_t sa, int64_t sb) {
+    const int axis = face >> 1, side = face & 1;
+    const int na = axis == 0 ? g.Y : g.X;
+    const int nb = axis == 2 ? g.Y : g.Z;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    const int a = blockIdx.y * blockDim.y + threadIdx.y;
+    if (a >= na || b >= nb) return;
+    int i, j, k;
+    if (axis == 0) { j = a; k = b; }
+    else if (axis == 1) { i = a; k = b; }
+    else { i = a; j = b; }
+    if (mode == 1) {  // unpack into ghost layer
+        if (axis == 0) i = side ? g.X : -1;
+        else if (axis == 1) j = side ? g.Y : -1;
+        else k = side ? g.Z : -1;
+        u[sidx(g, i, j, k)] = buf[(int64_t)a * nb + b];
+    } else {
+        if (axis == 0) i = side ? g.send_x1 : g.send_x0;
+        else if (axis == 1) j = side ? g.Y - 1 : 0;
+        else k = side ? g.Z - 1 : 0;
+        const double v = u[sidx(g, i, j, k)];
+        if (mode == 0) buf[(int64_t)a * nb + b] = v;
+        else buf[a * sa + b * sb] = v;
+    }
+}
+
+__global__ void k_publish(wave3d_peers peers, uint32_t epoch) {
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        for (int f = 0; f < 6; f++)
+            if (peers.flag_out[f]) st_release_sys(peers.flag_out[f], epoch);
+    }
+}
+
+// Stand-alone analytic error of a stored layer (two-stage max; ref K7).
+struct FErrParams {
+    int lo[3], hi[3];
+    int oz;
+    int64_t ps, pitch;
+    double arg_t;
+};
+__global__ void __launch_bounds__(256) k_field_error(FErrParams g, const double* u, const double* sx, const double* sy,
+                                                      const double* sz, unsigned long long* scratch, double* out) {
+    __shared__ double s_a[8], s_r[8];
+    __shared__ bool s_last;
+    const double c = cos(g.arg_t);
+    const int nk = g.hi[2] - g.lo[2] + 1, nj = g.hi[1] - g.lo[1] + 1, ni = g.hi[0] - g.lo[0] + 1;
+    const int64_t rows = (int64_t)ni * nj;
+    double ma = 0.0, mr = 0.0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // one warp per row, lanes stride along z
+    for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
+        const int i = g.lo[0] + (int)(row / nj), j = g.lo[1] + (int)(row % nj);
+        const double csy = __dmul_rn(__dmul_rn(c, sx[i]), sy[j]);
+        const double* r = u + (int64_t)(i + 1) * g.ps + (int64_t)(j + 1) * g.pitch + g.oz;
+        for (int k = g.lo[2] + lane; k < g.lo[2] + nk; k += 32) {
+            const double f = __dmul_rn(csy, sz[k]);
+            const double a = fabs(__dsub_rn(r[k], f));
+            ma = fmax(ma, a);
+            mr = fmax(mr, __ddiv_rn(a, fabs(f)));
+        }
+    }
+    ma = warp_max(ma);
+    mr = warp_max(mr);
+    if (lane == 0) { s_a[warp] = ma; s_r[warp] = mr; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) { ma = fmax(ma, s_a[w]); mr = fmax(mr, s_r[w]); }
+        scratch[2 + 2 * blockIdx.x] = (unsigned long long)__double_as_longlong(ma);
+        scratch[3 + 2 * blockIdx.x] = (unsigned long long)__double_as_longlong(mr);
+        __threadfence();
+        const unsigned long long ticket = atomicAdd(&scratch[0], 1ull);
+        s_last = ticket == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        double a = 0.0, r = 0.0;
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
+            a = fmax(a, __longlong_as_double((long long)((volatile unsigned long long*)scratch)[2 + 2 * b]));
+            r = fmax(r, __longlong_as_double((long long)((volatile unsigned long long*)scratch)[3 + 2 * b]));
+        }
+        a = warp_max(a);
+        r = warp_max(r);
+        __syncthreads();
+        if (lane == 0) { s_a[warp] = a; s_r[warp] = r; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < 8; w++) { a = fmax(a, s_a[w]); r = fmax(r, s_r[w]); }
+            out[0] = a;
+            out[1] = r;
+            scratch[0] = 0;  // ready for the next call
+        }
+    }
+}
+
+// ------------------------------------------------------------------ host side
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(f);
+    });
+    return fn;
+}
+
+int encode_field_map(CUtensorMap* map, const double* base, const wave3d_layout* lay, int box_w, int box_h) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) {
+        set_last_error("cuTensorMapEncodeTiled entry point not available");
+        return -1;
+    }
+    cuuint64_t dims[3] = {(cuuint64_t)lay->pitch, (cuuint64_t)lay->rows, (cuuint64_t)lay->planes};
+    cuuint64_t strides[2] = {(cuuint64_t)lay->pitch * 8, (cuuint64_t)lay->plane_stride * 8};
+    cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_last_error("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+        return -1;
+    }
+    return 0;
+}
+
+static bool is_pow2(double d) {
+    int e;
+    return std::frexp(d, &e) == 0.5;
+}
+static bool mant_all_ones(double d) {
+    uint64_t b;
+    memcpy(&b, &d, 8);
+    return (b & 0xFFFFFFFFFFFFFull) == 0xFFFFFFFFFFFFFull;
+}
+
+int choose_div_mode(const wave3d_problem* p) {
+    if (const char* e = getenv("WAVE3D_DIV")) {
+        int m = atoi(e);
+        if (m >= 0 && m <= 3) return m;
+    }
+    const double d[3] = {p->hx * p->hx, p->hy * p->hy, p->hz * p->hz};
+    if (is_pow2(d[0]) && is_pow2(d[1]) && is_pow2(d[2])) return 0;
+    for (double v : d)
+        if (mant_all_ones(v) || !(v > 1e-280 && v < 1e280)) return 3;
+    return 2;
+}
+
+int plan_smem_bytes(int ty, int tz, int s1, int s0) {
+    const int slot1 = ((ty + 2) * (tz + 4) * 8 + 127) & ~127;
+    const int slot0 = (ty * tz * 8 + 127) & ~127;
+    return 128 + s1 * slot1 + s0 * slot0 + 8 * (s1 + s0) + 64;
+}
+
+typedef void (*StepKernel)(const StepParams);
+
+template <int RJ>
+static StepKernel pick_rj(bool first, int div) {
+    switch ((first ? 4 : 0) + div) {
+        case 0: return k_step<RJ, false, 0>;
+        case 1: return k_step<RJ, false, 1>;
+        case 2: return k_step<RJ, false, 2>;
+        case 3: return k_step<RJ, false, 3>;
+        case 4: return k_step<RJ, true, 0>;
+        case 5: return k_step<RJ, true, 1>;
+        case 6: return k_step<RJ, true, 2>;
+        default: return k_step<RJ, true, 3>;
+    }
+}
+static StepKernel pick_kernel(int rj, bool first, int div) {
+    if (rj == 1) return pick_rj<1>(first, div);
+    if (rj == 2) return pick_rj<2>(first, div);
+    return pick_rj<4>(first, div);
+}
+
+// cudaFuncSetAttribute is per device; remember what was granted so that launches
+// inside a stream capture never have to call it.
+static int ensure_smem_attr(const void* k, int smem) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, int> granted;
+    int dev = 0;
+    W3D_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    int& g = granted[{dev, k}];
+    if (smem > g) {
+        W3D_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        g = smem;
+    }
+    return 0;
+}
+
+int prepare_step_kernels(const wave3d_plan* pl, int div) {
+    if (ensure_smem_attr((const void*)pick_kernel(pl->rj, false, div), plan_smem_bytes(pl->ty, pl->tz, pl->s1, pl->s0)))
+        return -1;
+    return ensure_smem_attr((const void*)pick_kernel(pl->rj, true, div), plan_smem_bytes(pl->ty, pl->tz, pl->s1, 0));
+}
+
+int step_occupancy(int rj, int warps, int smem_bytes) {
+    StepKernel k = pick_kernel(rj, false, 0);
+    if (cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)k, warps * 32, smem_bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return nb;
+}
+
+int launch_step(const StepLaunch& a) {
+    const wave3d_problem* pr = a.prob;
+    const wave3d_box* b = a.box;
+    const wave3d_layout* l = a.lay;
+    const wave3d_plan* pl = a.plan;
+    if (pl->rj != 1 && pl->rj != 2 && pl->rj != 4) {
+        set_last_error("plan.rj must be 1, 2 or 4");
+        return -1;
+    }
+    if (pl->warps < 1 || pl->warps > kMaxWarps || pl->ty != pl->rj * pl->warps || pl->tz != 64 || pl->s1 < 3 ||
+        pl->s0 < 1) {
+        set_last_error("invalid tile plan");
+        return -1;
+    }
+    StepParams p;
+    memset(&p, 0, sizeof p);
+    p.map_src = a.map_src;
+    p.map_io = a.map_io;
+    p.out = a.u_io;
+    p.sx = a.tabs[0]; p.sy = a.tabs[1]; p.sz = a.tabs[2];
+    p.rsx = a.tabs[3]; p.rsy = a.tabs[4]; p.rsz = a.tabs[5];
+    for (int f = 0; f < 6; f++) {
+        p.dst[f] = a.peers.dst[f];
+        p.sa[f] = a.peers.sa[f];
+        p.sb[f] = a.peers.sb[f];
+        p.flag_out[f] = a.peers.flag_out[f];
+        p.flag_in[f] = a.peers.flag_in[f];
+        if (p.dst[f]) p.push_mask |= 1u << f;
+    }
+    p.err = a.err + 2 * (size_t)a.n;
+    p.root_err = a.peers.root_err ? a.peers.root_err + 2 * (size_t)a.n : nullptr;
+    p.scratch = a.scratch;
+    p.desc = a.desc;
+    p.ps = l->plane_stride;
+    p.pitch = l->pitch;
+    p.coef = (pr->a2 * pr->tau) * pr->tau;  // ((a2*tau)*tau), *0.5 for the first step
+    if (a.first) p.coef = p.coef * 0.5;
+    p.arg_t = std::fma(pr->a_t * (double)a.n, pr->tau, pr->pi + pr->pi);
+    p.hx2 = pr->hx * pr->hx; p.hy2 = pr->hy * pr->hy; p.hz2 = pr->hz * pr->hz;
+    p.rx = 1.0 / p.hx2; p.ry = 1.0 / p.hy2; p.rz = 1.0 / p.hz2;
+    const double to = a.spin_timeout_s > 0 ? a.spin_timeout_s : 10.0;
+    p.timeout_ns = (unsigned long long)(to * 1e9);
+    p.oz = l->oz; p.X = b->n[0]; p.Y = b->n[1]; p.Z = b->n[2];
+    p.lo1 = b->lo[1]; p.hi1 = b->hi[1]; p.lo2 = b->lo[2]; p.hi2 = b->hi[2];
+    p.elo0 = b->elo[0]; p.ehi0 = b->ehi[0];
+    p.nty = pl->nty; p.ntz = pl->ntz; p.nchunks = pl->nchunks; p.ty = pl->ty; p.tz = pl->tz;
+    p.s1 = pl->s1; p.s0 = pl->s0;
+    p.send_x0 = b->send_x[0]; p.send_x1 = b->send_x[1];
+    p.epoch_wait = (uint32_t)a.n;       // neighbours published layer n-1 as epoch n
+    p.epoch_pub = (uint32_t)a.n + 1u;
+    const int div = a.div_mode >= 0 ? a.div_mode : choose_div_mode(pr);
+    StepKernel k = pick_kernel(pl->rj, a.first != 0, div);
+    const int smem = plan_smem_bytes(pl->ty, pl->tz, pl->s1, a.first ? 0 : pl->s0);
+    if (ensure_smem_attr((const void*)k, smem)) return -1;
+    const int grid = pl->nty * pl->ntz * pl->nchunks;
+    k<<<grid, pl->warps * 32, smem, a.stream>>>(p);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace w3d
+
+// ----------------------------------------------------------------- C entry points
+using namespace w3d;
+
+extern "C" {
+
+const char* wave3d_cuda_last_error(void) { return g_last_error.c_str(); }
+
+int wave3d_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+int wave3d_cuda_available(void) { return wave3d_cuda_device_count() > 0; }
+
+int wave3d_cuda_tables(const wave3d_problem* p, const wave3d_box* b, double* sx, double* sy, double* sz, double* rsx,
+                       double* rsy, double* rsz, void* stream) {
+    TabParams tp;
+    tp.pi = p->pi; tp.hx = p->hx; tp.hy = p->hy; tp.hz = p->hz; tp.Lx = p->Lx; tp.Ly = p->Ly; tp.Lz = p->Lz;
+    int nmax = 0;
+    for (int a = 0; a < 3; a++) {
+        tp.n[a] = b->n[a];
+        tp.o[a] = b->o[a];
+        nmax = nmax > b->n[a] ? nmax : b->n[a];
+    }
+    dim3 grid((nmax + 127) / 128, 3);
+    k_tables<<<grid, 128, 0, (cudaStream_t)stream>>>(tp, sx, sy, sz, rsx, rsy, rsz);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}
+
+int wave3d_cuda_layer0(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l, const double* sx,
+                       const double* sy, const double* sz, double* u0, void* stream) {
+    dim3 block(64, 4);
+    dim3 grid((b->n[2] + 63) / 64, (b->n[1] + 3) / 4, b->n[0] < 64 ? b->n[0] : 64);
+    const double arg_t = std::fma(p->a_t * 0.0, p->tau, p->pi + p->pi);
+    k_layer0<<<grid, block, 0, (cudaStream_t)stream>>>(u0, sx, sy, sz, arg_t, b->n[0], b->n[1], b->n[2],
+                                                        l->plane_stride, l->pitch, l->oz);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}
+
+int wave3d_cuda_zero_walls(const wave3d_box* b, const wave3d_layout* l, double* u, void* stream) {
+    int mask = 0;
+    if (b->coords[1] == 0) mask |= 1;
+    if (b->coords[1] == b->dims[1] - 1) mask |= 2;
+    if (b->coords[2] == 0) mask |= 4;
+    if (b->coords[2] == b->dims[2] - 1) mask |= 8;
+    if (!mask) return 0;
+    const int m = b->n[1] > b->n[2] ? b->n[1] : b->n[2];
+    dim3 grid((m + 127) / 128, b->n[0]);
+    k_zero_walls<<<grid, 128, 0, (cudaStream_t)stream>>>(u, b->n[0], b->n[1], b->n[2], l->plane_stride, l->pitch, l->oz,
+                                                          mask);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int face_launch(const wave3d_box* b, const wave3d_layout* l, double* u, int face, int mode, double* buf,
+                       int64_t sa, int64_t sb, cudaStream_t stream) {
+    FaceParams g;
+    g.X = b->n[0]; g.Y = b->n[1]; g.Z = b->n[2]; g.oz = l->oz;
+    g.ps = l->plane_stride; g.pitch = l->pitch;
+    g.send_x0 = b->send_x[0]; g.send_x1 = b->send_x[1];
+    const int axis = face >> 1;
+    const int na = axis == 0 ? g.Y : g.X;
+    const int nb = axis == 2 ? g.Y : g.Z;
+    dim3 block(64, 4);
+    dim3 grid((nb + 63) / 64, (na + 3) / 4);
+    k_face<<<grid, block, 0, stream>>>(g, u, face, mode, buf, sa, sb);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}
+
+int wave3d_cuda_pack_face(const wave3d_box* b, const wave3d_layout* l, const double* u, int face, double* buf,
+                          void* stream) {
+    return face_launch(b, l, const_cast<double*>(u), face, 0, buf, 0, 0, (cudaStream_t)stream);
+}
+int wave3d_cuda_unpack_face(const wave3d_box* b, const wave3d_layout* l, double* u, int face, const double* buf,
+                            void* stream) {
+    return face_launch(b, l, u, face, 1, const_cast<double*>(buf), 0, 0, (cudaStream_t)stream);
+}
+int wave3d_cuda_push_faces(const wave3d_box* b, const wave3d_layout* l, const double* u, const wave3d_peers* peers,
+                           uint32_t epoch, void* stream) {
+    for (int f = 0; f < 6; f++) {
+        if (!peers->dst[f]) continue;
+        if (face_launch(b, l, const_cast<double*>(u), f, 2, peers->dst[f], peers->sa[f], peers->sb[f],
+                        (cudaStream_t)stream))
+            return -1;
+    }
+    bool any = false;
+    for (int f = 0; f < 6; f++) any = any || peers->flag_out[f];
+    if (any) {
+        k_publish<<<1, 32, 0, (cudaStream_t)stream>>>(*peers, epoch);
+        W3D_TRY(cudaGetLastError());
+    }
+    return 0;
+}
+
+int64_t wave3d_cuda_field_error_scratch_words(const wave3d_box* b) {
+    (void)b;
+    return 2 + 2 * 1184;  // ticket + pad, then (abs, rel) per block; grid is capped at 8 CTAs x 148 SMs
+}
+
+int wave3d_cuda_field_error(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l,
+                            const double* const tabs[6], const double* u, int n, uint64_t* scratch, double* out,
+                            void* stream) {
+    FErrParams g;
+    for (int a = 0; a < 3; a++) {
+        g.lo[a] = b->elo[a];
+        g.hi[a] = b->ehi[a];
+    }
+    g.oz = l->oz; g.ps = l->plane_stride; g.pitch = l->pitch;
+    g.arg_t = std::fma(p->a_t * (double)n, p->tau, p->pi + p->pi);
+    const int64_t rows = (int64_t)(g.hi[0] - g.lo[0] + 1) * (g.hi[1] - g.lo[1] + 1);
+    int64_t blocks = (rows + 7) / 8;
+    if (blocks > 1184) blocks = 1184;
+    if (blocks < 1) blocks = 1;
+    k_field_error<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(g, u, tabs[0], tabs[1], tabs[2],
+                                                                 reinterpret_cast<unsigned long long*>(scratch), out);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}
+
+int wave3d_cuda_step(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l, const wave3d_plan* plan,
+                     const double* const tabs[6], const double* u1, double* u_io, int n, int first,
+                     const wave3d_peers* peers, uint64_t* err, uint32_t* scratch, double spin_timeout_s,
+                     void* stream) {
+    StepLaunch a;
+    memset(&a, 0, sizeof a);
+    if (encode_field_map(&a.map_src, u1, l, plan->tz + 4, plan->ty + 2)) return -1;
+    if (encode_field_map(&a.map_io, u_io, l, plan->tz, plan->ty)) return -1;
+    a.prob = p; a.box = b; a.lay = l; a.plan = plan;
+    for (int i = 0; i < 6; i++) a.tabs[i] = tabs[i];
+    a.u_io = u_io; a.n = n; a.first = first;
+    if (peers) a.peers = *peers;
+    a.err = err; a.scratch = scratch; a.spin_timeout_s = spin_timeout_s;
+    a.div_mode = -1;
+    a.stream = (cudaStream_t)stream;
+    return launch_step(a);
+}
+
+}  // extern "C"
