@@ -1,0 +1,190 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of wave3d-b200 (contract in the task statement / BASELINE.json).
+
+Metric  : Gcell-updates/s = (N+1)^3 * timesteps / t_solve / 1e9, t_solve device-timed (CUDA events)
+          over what the reference's started->finished events span (layer 0, every update, every
+          error evaluation, every halo exchange; ref: cuda_sol.cpp:382,422-425), MAX over ranks.
+Config  : BASELINE.json config 3 — N=512, Lx=Ly=Lz=1, tau=0.025/20, strong scaling over 1/2/4/8 GPUs.
+          `--steps K` = timesteps (T = K*tau). fp64 (the reference's precision; bf16 does not apply).
+Launch  : python bench.py --gpus 1 ...            (single process)
+          python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...   (one rank per GPU)
+          python bench.py --impl reference ...    (unmodified reference from baseline/_ref)
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+TAU = 0.025 / 20  # BASELINE.json config 1/3: T=0.025 over 20 steps
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=512, help="grid intervals per axis (BASELINE config 3: 512)")
+    ap.add_argument("--length", default="1", help="box length: a number or 'pi'")
+    ap.add_argument("--dims", default=None, help="force the process grid, e.g. 8x1x1")
+    ap.add_argument("--transport", default="auto", choices=["auto", "peer", "staged"])
+    ap.add_argument("--repeats", type=int, default=5, help="timed K-step solves; the median is reported")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def world():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def flush_l2(torch, dev):
+    # write a buffer larger than the 126 MB L2 between timed solves (inputs are >> L2 anyway at N=512)
+    buf = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+    buf.zero_()
+    torch.cuda.synchronize(dev)
+    del buf
+
+
+def run_ours(a):
+    import torch
+    import wave3d_b200 as w
+    from wave3d_b200 import _lib
+    from wave3d_b200.utils.clocks import ClockSampler
+    rank, ws = world()
+    L = _lib.PI_FULL if a.length == "pi" else float(a.length)
+    N = a.n
+    if a.scaling == "weak":  # per-GPU work fixed: N grows with the cube root of the GPU count
+        N = int(round((a.n + 1) * (a.gpus ** (1.0 / 3.0)))) - 1
+    K = a.steps
+    p = w.Problem(N=N, Np=a.gpus, Lx=L, Ly=L, Lz=L, T=K * TAU, timesteps=K)
+    dims = w.parallel.decomp.parse_dims(a.dims) if a.dims else None
+    distributed = ws > 1
+    if distributed:
+        from wave3d_b200.parallel import dist as pdist
+        pdist.init_process_group_from_env("nccl")
+        solver = w.DistributedWaveSolver(p, dims=dims, transport=a.transport)
+        dev = solver.device
+        inner = solver.inner
+        transport = solver.transport
+    else:
+        solver = w.WaveSolver(p, nranks=a.gpus, dims=dims, backend="cuda",
+                              transport="peer" if a.transport == "auto" else a.transport,
+                              devices=list(range(a.gpus)))
+        dev = torch.device("cuda", 0)
+        inner = solver
+        transport = solver.transport
+    import torch.distributed as dist
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if distributed:
+            dist.barrier()
+
+    # ---- warm-up: at least W untimed steps (whole solves, so every kernel variant and the graph are warm)
+    nwarm = max(1, -(-a.warmup // K))
+    for _ in range(nwarm):
+        solver.run()
+    # ---- timed: `repeats` brackets of exactly K steps each, device-timed inside run(), max over ranks
+    times, launches, res = [], 0, None
+    with ClockSampler(dev.index or 0, 0.02) as clk:
+        for _ in range(max(1, a.repeats)):
+            flush_l2(torch, dev)
+            barrier()
+            res = solver.run()  # barrier + sync on both sides inside (distributed) / stream sync (single)
+            barrier()
+            times.append(res.solve_ms)
+            launches = res.launches
+    clocks = clk.summary()
+    t_ms = statistics.median(times)
+    cells = float(N + 1) ** 3
+    value = cells * K / (t_ms * 1e-3) / 1e9
+
+    # ---- end to end through the public per-step API: every step uploads its descriptor from pinned host
+    # memory (H2D), runs the fused kernel, and reads the step's error maxima back (D2H) before the next step
+    e2e = None
+    if not a.no_e2e:
+        desc = torch.empty((K + 1, 2), dtype=torch.float64).pin_memory()
+        for n in range(1, K + 1):
+            desc[n, 0], desc[n, 1] = inner.step_descriptor(n)
+        e2e_times = []
+        for rep in range(3):
+            if distributed:
+                solver._reset()
+            else:
+                solver.reset()
+            barrier()
+            t0 = time.perf_counter()
+            inner.enqueue_layer0()
+            if transport == "staged":
+                (solver.halo.exchange(0) if distributed else inner.exchange_local(0))
+            errs = []
+            for n in range(1, K + 1):
+                inner.enqueue_step_e2e(n, desc[n].data_ptr())
+                if transport == "staged" and n < K:
+                    (solver.halo.exchange(n) if distributed else inner.exchange_local(n))
+                errs.append(inner.layer_error(n))
+            barrier()
+            e2e_times.append((time.perf_counter() - t0) * 1e3)
+        t_e2e = statistics.median(e2e_times[1:]) if len(e2e_times) > 1 else e2e_times[0]
+        if distributed:
+            tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t_e2e = float(tt.item())
+        e2e = {"value": cells * K / (t_e2e * 1e-3) / 1e9, "unit": "Gcell-updates/s", "h2d_bytes_per_step": 16,
+               "d2h_bytes_per_step": 16, "ms_per_step": t_e2e / K,
+               "note": "per step: pinned->device copy of the step descriptor, fused kernel, device->host read of "
+                       "the step's max abs/rel error, stream sync; wall clock, max over ranks"}
+    out = {
+        "metric": "Gcell-updates/s (device-timed, max over ranks)", "value": value, "unit": "Gcell-updates/s",
+        "n_gpus": a.gpus, "steps": K, "warmup": a.warmup, "ms_per_step": t_ms / K, "higher_is_better": True,
+        "scaling": a.scaling, "vs_baseline": None, "dtype": "fp64", "data": "synthetic (analytic initial condition)",
+        "impl": "ours",
+        "config": {"model": f"wave3d N={N} L={a.length} tau={TAU} timesteps={K}", "global_batch": int(cells),
+                   "seq_len": K, "parallelism": "x".join(str(d) for d in (res.dims if res else (1, 1, 1))),
+                   "transport": transport, "l2": "inputs larger than L2 (2 fields x %.0f MB per GPU) + 256 MB flush "
+                   "between timed solves" % (cells * 8 / 1e6 / max(1, a.gpus)),
+                   "repeats": len(times), "stat": "median", "solve_ms_all": [round(t, 4) for t in times],
+                   "plan": res.extra.get("plan") if res else None,
+                   "max_abs_error_last_layer": res.max_abs[-1] if res else None,
+                   "max_rel_error_last_layer": res.max_rel[-1] if res else None},
+        "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
+                   "reasons": clocks.get("reasons", []), "samples": clocks.get("samples")},
+        "gpu_launches": int(launches),
+    }
+    if e2e:
+        out["e2e"] = e2e
+    if distributed:
+        solver.close()
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        dist.destroy_process_group()
+    else:
+        solver.close()
+        print(json.dumps(out), flush=True)
+
+
+def run_reference(a):
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    try:
+        import run_reference as rr
+    except Exception as e:  # noqa: BLE001
+        rank, _ = world()
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": f"baseline/run_reference.py not importable: {e}"}))
+        return
+    rr.bench(a, TAU)
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

@@ -81,6 +81,7 @@ struct wave3d_solver {
     int64_t launches = 0;
     double* pinned = nullptr;  // 2 doubles per layer per local rank (per-step readback) + descriptors
     double exchange_ms = 0.0;
+    bool fresh = false;  // reset() was called and nothing ran since
 };
 
 namespace {
@@ -576,6 +577,7 @@ int wave3d_solver_reset(wave3d_solver* s) {
         std::fill(r.habs.begin(), r.habs.end(), 0.0);
         std::fill(r.hrel.begin(), r.hrel.end(), 0.0);
     }
+    s->fresh = true;
     if (s->opts.backend != WAVE3D_BACKEND_CUDA) return 0;
     for (auto& r : s->ranks) {
         if (use_device(r.device)) return -1;
@@ -584,10 +586,12 @@ int wave3d_solver_reset(wave3d_solver* s) {
         W3D_TRY(cudaMemsetAsync(r.flags, 0, 256, st));
         W3D_TRY(cudaMemsetAsync(r.scratch, 0, 256, st));
     }
+    s->fresh = true;
     return wave3d_solver_sync(s);
 }
 
 int wave3d_solver_enqueue_layer0(wave3d_solver* s) {
+    s->fresh = false;
     if (s->opts.backend == WAVE3D_BACKEND_CUDA) {
         for (auto& r : s->ranks)
             if (enqueue_layer0_rank(s, r)) return -1;
@@ -785,7 +789,10 @@ static int enqueue_all(wave3d_solver* s, Group* only) {
 
 int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
     if (t) memset(t, 0, sizeof *t);
-    if (wave3d_solver_reset(s)) return -1;
+    // Across processes the caller resets every rank and then barriers (a neighbour's
+    // late flag must not be wiped, an early one must not be lost); otherwise reset here.
+    if (!s->fresh && wave3d_solver_reset(s)) return -1;
+    s->fresh = false;
     if (s->opts.backend != WAVE3D_BACKEND_CUDA) {
         if (!s->all_local) return -1;
         auto t0 = std::chrono::steady_clock::now();

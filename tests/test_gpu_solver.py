@@ -1,0 +1,139 @@
+"""End-to-end solves on the GPU: accuracy vs BASELINE.md, decomposition invariance with several
+ranks time-sharing one GPU (peer transport: in-kernel ghost stores + epoch flags), staged transport,
+CUDA graph vs eager, per-step mode, the CLI binary (SURVEY §4.2 integration / invariance rows)."""
+import os
+import subprocess
+
+import pytest
+import torch
+
+import wave3d_b200 as w
+from wave3d_b200 import _lib
+
+from conftest import BASELINE_CUDA_EMULATED
+
+pytestmark = pytest.mark.gpu
+
+
+def _problem(key):
+    N, Lx, Ly, Lz, T, steps = key
+    f = lambda v: _lib.PI_FULL if v == "pi" else v
+    return w.Problem(N=N, Lx=f(Lx), Ly=f(Ly), Lz=f(Lz), T=T, timesteps=steps)
+
+
+@pytest.mark.parametrize("key", list(BASELINE_CUDA_EMULATED))
+def test_accuracy_vs_emulated_reference(key):
+    p = _problem(key)
+    with w.WaveSolver(p, nranks=1, backend="cuda") as s:
+        res = s.run()
+        assert s.status() == 0
+    assert res.max_abs[0] == 0.0 and res.max_rel[0] == 0.0
+    for layer, (ea, er) in BASELINE_CUDA_EMULATED[key].items():
+        # libdevice vs glibc sin/cos differ in the last bits of f: ~1e-7 relative on the abs maximum
+        assert abs(res.max_abs[layer] - ea) <= 2e-6 * ea, (layer, res.max_abs[layer], ea)
+    # second-order accuracy sanity: abs error grows ~ n^2
+    assert 300 < res.max_abs[20] / res.max_abs[1] < 500
+
+
+def test_gpu_equals_cpu_backend_when_tables_agree():
+    """With identical sine tables the GPU field is bit-identical to the CPU twin, so the maxima may only
+    differ through libdevice-vs-libm table bits; they must agree to ~1e-7 and be identical in count."""
+    p = w.Problem(N=48, Lx=1.0, Ly=2.0, Lz=3.0, T=0.05, timesteps=10)
+    with w.WaveSolver(p, backend="cpu") as c, w.WaveSolver(p, backend="cuda") as g:
+        rc, rg = c.run(), g.run()
+    for n in range(1, 11):
+        assert abs(rc.max_abs[n] - rg.max_abs[n]) <= 2e-6 * rc.max_abs[n]
+
+
+SHAPES = [(2, None), (4, None), (8, None), (8, (8, 1, 1)), (8, (1, 2, 4)), (6, None), (3, (1, 1, 3)), (12, (2, 3, 2))]
+
+
+@pytest.mark.parametrize("nranks,dims", SHAPES)
+def test_decomposition_invariance_peer_transport(nranks, dims):
+    """Ranks time-share GPU 0 (launched layer by layer, so no kernel ever waits on a later launch):
+    exercises ghost stores, seam planes, walls and the flag protocol. Maxima must be bit-identical."""
+    p = w.Problem(N=45, Lx=1.0, Ly=2.0, Lz=_lib.PI_FULL, T=0.05, timesteps=8)
+    with w.WaveSolver(p, nranks=1, backend="cuda") as s:
+        ref = s.run()
+    with w.WaveSolver(p, nranks=nranks, dims=dims, backend="cuda", devices=[0]) as s:
+        res = s.run()
+        assert s.status() == 0
+    assert res.max_abs == ref.max_abs
+    assert res.max_rel == ref.max_rel
+
+
+@pytest.mark.parametrize("nranks,dims", [(2, None), (8, None), (4, (1, 4, 1))])
+def test_staged_transport_equals_peer(nranks, dims):
+    p = w.Problem(N=40, T=0.05, timesteps=6)
+    with w.WaveSolver(p, nranks=nranks, dims=dims, backend="cuda", devices=[0]) as s:
+        a = s.run()
+    with w.WaveSolver(p, nranks=nranks, dims=dims, backend="cuda", devices=[0], transport="staged") as s:
+        b = s.run()
+    assert a.max_abs == b.max_abs and a.max_rel == b.max_rel
+
+
+def test_graph_equals_eager_and_repeatable():
+    p = w.Problem(N=64, T=0.025, timesteps=10)
+    with w.WaveSolver(p, nranks=2, backend="cuda", devices=[0], use_graph=True) as s:
+        a1, a2 = s.run(), s.run()
+    with w.WaveSolver(p, nranks=2, backend="cuda", devices=[0], use_graph=False) as s:
+        b = s.run()
+    assert a1.max_abs == a2.max_abs == b.max_abs
+    assert a1.max_rel == a2.max_rel == b.max_rel
+    assert a1.launches == b.launches > p.timesteps
+
+
+def test_per_step_mode_and_e2e_descriptor():
+    p = w.Problem(N=64, T=0.025, timesteps=6)
+    with w.WaveSolver(p, backend="cuda") as s:
+        ref = s.run()
+        per = s.run_per_step()
+        assert per.max_abs == ref.max_abs and per.max_rel == ref.max_rel
+        # end-to-end flavour: the step descriptor is uploaded from pinned memory every step
+        desc = torch.empty((p.timesteps + 1, 2), dtype=torch.float64).pin_memory()
+        for n in range(1, p.timesteps + 1):
+            desc[n, 0], desc[n, 1] = s.step_descriptor(n)
+        s.reset()
+        s.enqueue_layer0()
+        got = [(0.0, 0.0)]
+        for n in range(1, p.timesteps + 1):
+            s.enqueue_step_e2e(n, desc[n].data_ptr())
+            got.append(s.layer_error(n))
+        assert [g[0] for g in got] == ref.max_abs and [g[1] for g in got] == ref.max_rel
+
+
+def test_field_views_are_live():
+    p = w.Problem(N=24, T=0.025, timesteps=3)
+    with w.WaveSolver(p, backend="cuda") as s:
+        s.run()
+        f1 = s.field(0, 1)  # layer 3 lives in field 1
+        from wave3d_b200.ops import kernels as K
+        box, lay = s.box(0), s.layout(0)
+        tabs = K.tables(p, box, "cuda:0")
+        a, r = K.field_error(p, box, lay, tabs, f1, 3)
+        ea, er = s.errors()
+        assert (a, r) == (ea[3], er[3])
+
+
+def test_cli_binary_writes_reference_format(tmp_path):
+    exe = os.path.join(_lib.REPO, "bin", "wave3d")
+    out = subprocess.run([exe, "64", "1", "pi", "pi", "pi", "0.025", "20"], cwd=tmp_path, capture_output=True,
+                         text=True, env={**os.environ, "WAVE3D_FULL_PRECISION": "1"})
+    assert out.returncode == 0, out.stderr
+    assert out.stdout.splitlines()[0] == "C = 0.00405285"
+    txt = (tmp_path / "output_N64_Np1.txt").read_text().splitlines()
+    assert txt[0].startswith("initialization done in ") and txt[0].endswith("ms")
+    assert txt[1].startswith("numerical solution calculated in ")
+    assert txt[2] == "max abs and rel errors on layer 0: 0 0"
+    assert txt[3].startswith("max abs and rel errors on layer 1: 7.15")
+    assert len(txt) == 2 + 21 + 4
+    full = (tmp_path / "output_N64_Np1.txt.full").read_text().splitlines()
+    v = float(full[22].split()[-2])
+    assert abs(v - 2.8600414148094444e-08) < 2e-6 * v
+
+
+def test_cli_multi_rank_on_one_gpu(tmp_path):
+    exe = os.path.join(_lib.REPO, "bin", "wave3d")
+    out = subprocess.run([exe, "40", "4", "1", "1", "1", "0.025", "5"], cwd=tmp_path, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert (tmp_path / "output_N40_Np4.txt").exists()

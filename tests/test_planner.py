@@ -1,0 +1,32 @@
+"""Tile planner sanity (host-only model)."""
+import ctypes as C
+
+import pytest
+
+import wave3d_b200 as w
+from wave3d_b200 import _lib
+from wave3d_b200.ops import kernels as K
+from wave3d_b200.parallel.decomp import Decomposition
+
+
+@pytest.mark.parametrize("N,nranks,dims", [(512, 1, None), (512, 8, None), (256, 1, None), (1024, 8, (8, 1, 1)),
+                                           (2048, 8, None), (33, 1, None), (100, 4, (1, 2, 2))])
+def test_plan_is_feasible(N, nranks, dims):
+    dec = Decomposition.create(N, nranks, dims)
+    for r in {0, nranks - 1}:
+        box = dec.box(r)
+        pl = K.plan_for(box, 148)
+        assert pl.tz == 64 and pl.rj in (1, 2, 4) and 2 <= pl.warps <= 16 and pl.ty == pl.rj * pl.warps
+        assert pl.nty * pl.ty >= box.hi[1] - box.lo[1] + 1
+        assert pl.ntz * pl.tz >= box.hi[2] - box.lo[2] + 1
+        assert 1 <= pl.nchunks <= max(1, box.n[0] // 8)
+        assert pl.smem_bytes <= 227 * 1024 and pl.s1 >= 3 and pl.s0 >= 1
+        assert pl.ctas == pl.nty * pl.ntz * pl.nchunks
+        assert (0.3 if N >= 100 else 0.0) < pl.efficiency <= 1.0
+
+
+def test_plan_override(monkeypatch):
+    monkeypatch.setenv("WAVE3D_TILE", "16,2,3")
+    box = Decomposition.create(256, 1).box(0)
+    pl = K.plan_for(box, 148)
+    assert (pl.ty, pl.rj, pl.warps, pl.nchunks) == (16, 2, 8, 3)
