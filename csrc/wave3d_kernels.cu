@@ -142,21 +142,53 @@ __device__ __forceinline__ double div_const(double x, double d, double r) {
     }
 }
 
+// ---- shared-memory access by 32-bit shared address (keeps LDS, never generic LD)
+__device__ __forceinline__ double2 lds2(uint32_t a) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double lds1(uint32_t a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
 struct ErrAcc {
     double mabs, mrel, best, thr;
 };
 
-// Error bookkeeping for one cell. cand approximates a/|f| to ~1e-15 relative via
-// reciprocal tables; the exact division runs only if cand can still be the maximum
-// (band 2^-40 >> table error), so the result equals max over all cells of the
-// reference's `abs_error / fabs(f)` (ref: cuda_sol_kernels.cu:42-45).
-__device__ __forceinline__ void err_cell(ErrAcc& e, double u, double f, double rxy, double rszk) {
-    const double a = fabs(__dsub_rn(u, f));
-    e.mabs = fmax(e.mabs, a);
-    const double cand = __dmul_rn(__dmul_rn(a, rxy), rszk);
-    if (cand >= e.thr) {
-        e.mrel = fmax(e.mrel, __ddiv_rn(a, fabs(f)));
-        e.best = fmax(e.best, cand);
+// max that ignores a NaN candidate (the reference's fmax / host '>' semantics) in 3 instructions
+__device__ __forceinline__ double max_keep(double m, double v) { return v > m ? v : m; }
+
+// Error bookkeeping of one row (1 or 2 cells). cand approximates a/|f| to ~1e-15 relative via
+// reciprocal tables; the exact IEEE division runs only when a cell can still be the maximum
+// (band 2^-40 >> table error), so the result equals max over all cells of the reference's
+// `abs_error / fabs(f)` (ref: cuda_sol_kernels.cu:42-45).
+template <bool TWO>
+__device__ __forceinline__ void err_row(ErrAcc& e, double ua, double ub, double fxy, double rxy, double sz0, double sz1,
+                                        double rz0, double rz1) {
+    const double fa = __dmul_rn(fxy, sz0);
+    const double aa = fabs(__dsub_rn(ua, fa));
+    e.mabs = max_keep(e.mabs, aa);
+    const double ca = __dmul_rn(__dmul_rn(aa, rxy), rz0);
+    double fb = 0.0, ab = 0.0, cb = 0.0;
+    if (TWO) {
+        fb = __dmul_rn(fxy, sz1);
+        ab = fabs(__dsub_rn(ub, fb));
+        e.mabs = max_keep(e.mabs, ab);
+        cb = __dmul_rn(__dmul_rn(ab, rxy), rz1);
+    }
+    if (ca >= e.thr || (TWO && cb >= e.thr)) {
+        e.mrel = fmax(e.mrel, __ddiv_rn(aa, fabs(fa)));
+        e.best = fmax(e.best, ca);
+        if (TWO) {
+            e.mrel = fmax(e.mrel, __ddiv_rn(ab, fabs(fb)));
+            e.best = fmax(e.best, cb);
+        }
         e.thr = e.best * (1.0 - 0x1p-40);
     }
 }
@@ -167,88 +199,71 @@ __device__ __forceinline__ double warp_max(double v) {
     return v;
 }
 
-__device__ __forceinline__ void store_pair(double* p, double a, double b, bool v0, bool v1) {
-    if (v1 && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+__device__ __forceinline__ void store_pair(double* p, double a, double b, bool two) {
+    if (two && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
         *reinterpret_cast<double2*>(p) = make_double2(a, b);
     } else {
-        if (v0) p[0] = a;
-        if (v1) p[1] = b;
+        p[0] = a;
+        if (two) p[1] = b;
     }
 }
 
-constexpr int kMaxWarps = 16;
+// Face cells are stored a second time, straight into the neighbour's ghost cells (peer memory).
+__device__ __noinline__ void push_row(const StepParams& p, int i, int j, int kk, double ua, double ub, bool two) {
+    if ((p.push_mask & 1u) && i == p.send_x0) store_pair(p.dst[0] + j * p.sa[0] + kk, ua, ub, two);
+    if ((p.push_mask & 2u) && i == p.send_x1) store_pair(p.dst[1] + j * p.sa[1] + kk, ua, ub, two);
+    if ((p.push_mask & 4u) && j == 0) store_pair(p.dst[2] + i * p.sa[2] + kk, ua, ub, two);
+    if ((p.push_mask & 8u) && j == p.Y - 1) store_pair(p.dst[3] + i * p.sa[3] + kk, ua, ub, two);
+    if ((p.push_mask & 16u) && kk == 0) p.dst[4][i * p.sa[4] + j * p.sb[4]] = ua;
+    if ((p.push_mask & 32u) && kk == p.Z - 1) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ua;
+    if ((p.push_mask & 32u) && two && kk + 1 == p.Z - 1) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ub;
+}
+
+constexpr int kMaxWarps = 11;   // compute warps per CTA (one more warp is the TMA producer): 384 threads max
+constexpr int kTZ = 64;         // tile width in z: one warp row = 32 lanes x 2 cells
+constexpr int kW1 = kTZ + 4;    // halo slot row length in doubles (2 halo columns each side keep 16-byte alignment)
 
 template <int RJ, bool FIRST, int DIV>
-__global__ void __launch_bounds__(kMaxWarps * 32, 1) k_step(const __grid_constant__ StepParams p) {
-    extern __shared__ unsigned char smem_raw[];
+__global__ void __launch_bounds__((kMaxWarps + 1) * 32, 1) k_step(const __grid_constant__ StepParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_bcast[3];
     __shared__ double s_red[kMaxWarps][2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W1 = p.tz + 4;                                     // halo slot row length (doubles)
-    const uint32_t slot1_bytes = (uint32_t)(((p.ty + 2) * W1 * 8 + 127) & ~127);
-    const uint32_t slot0_bytes = (uint32_t)((p.ty * p.tz * 8 + 127) & ~127);
-    const uint32_t box1_bytes = (uint32_t)((p.ty + 2) * W1 * 8);
-    const uint32_t box0_bytes = (uint32_t)(p.ty * p.tz * 8);
+    const int ncw = (int)(blockDim.x >> 5) - 1;  // compute warps
+    const uint32_t slot1_bytes = (uint32_t)(((p.ty + 2) * kW1 * 8 + 127) & ~127);
+    const uint32_t slot0_bytes = (uint32_t)((p.ty * kTZ * 8 + 127) & ~127);
+    const uint32_t ring1 = (smem_u32(smem_raw) + 127u) & ~127u;
+    const uint32_t ring0 = ring1 + (uint32_t)p.s1 * slot1_bytes;
+    const uint32_t bars = ring0 + (uint32_t)(FIRST ? 0 : p.s0) * slot0_bytes;
+    const uint32_t full1 = bars, empty1 = full1 + 8u * (uint32_t)p.s1;
+    const uint32_t full0 = empty1 + 8u * (uint32_t)p.s1, empty0 = full0 + 8u * (uint32_t)p.s0;
 
-    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-    unsigned char* ring1 = base;
-    unsigned char* ring0 = ring1 + (size_t)p.s1 * slot1_bytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(ring0 + (size_t)(FIRST ? 0 : p.s0) * slot0_bytes);
-    const uint32_t bar1 = smem_u32(bars);              // full barriers of ring1
-    const uint32_t bar0 = bar1 + 8u * (uint32_t)p.s1;  // full barriers of ring0
-
-    // ---- work item
+    // ---- work item: (z tile, y tile, x chunk)
     const int bid = blockIdx.x;
     const int tzi = bid % p.ntz;
     const int tyi = (bid / p.ntz) % p.nty;
     const int cxi = bid / (p.ntz * p.nty);
     const int j0 = p.lo1 + tyi * p.ty;
-    const int k0 = p.lo2 + tzi * p.tz;
+    const int k0 = p.lo2 + tzi * kTZ;
     const int xa = (int)(((int64_t)p.X * cxi) / p.nchunks);
     const int xb = (int)(((int64_t)p.X * (cxi + 1)) / p.nchunks);
     const int nplanes = xb - xa;
 
-    // TMA box origins in storage coordinates
-    const int c0_src = p.oz + k0 - 2, c1_src = j0;  // row(j0) - 1 = j0
-    const int c0_io = p.oz + k0, c1_io = j0 + 1;
-
     if (tid == 0) {
-        // Neighbours must have finished the previous layer: their ghost stores are
-        // complete (RAW) and they no longer read the ghosts we are about to overwrite (WAR).
-        const unsigned long long t0 = globaltimer_ns();
-        for (int f = 0; f < 6; f++) {
-            const uint32_t* fl = p.flag_in[f];
-            if (!fl) continue;
-            while (ld_acquire_sys(fl) < p.epoch_wait) {
-                __nanosleep(64);
-                if (globaltimer_ns() - t0 > p.timeout_ns) {
-                    atomicExch(&p.scratch[1], 1u);
-                    break;
-                }
-            }
+        for (int s = 0; s < p.s1; s++) {
+            mbar_init(full1 + 8u * s, 1);
+            mbar_init(empty1 + 8u * s, (uint32_t)ncw);
         }
-        asm volatile("fence.proxy.async;" ::: "memory");
-        for (int s = 0; s < p.s1; s++) mbar_init(bar1 + 8u * s, 1);
         if (!FIRST)
-            for (int s = 0; s < p.s0; s++) mbar_init(bar0 + 8u * s, 1);
+            for (int s = 0; s < p.s0; s++) {
+                mbar_init(full0 + 8u * s, 1);
+                mbar_init(empty0 + 8u * s, (uint32_t)ncw);
+            }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        // prologue loads: source planes xa-1 .. , in-place planes xa ..
-        const int n1 = min(p.s1, nplanes + 2);
-        for (int q = 0; q < n1; q++) {
-            mbar_expect_tx(bar1 + 8u * q, box1_bytes);
-            tma_load_3d(smem_u32(ring1 + (size_t)q * slot1_bytes), &p.map_src, c0_src, c1_src, xa + q, bar1 + 8u * q);
-        }
-        if (!FIRST) {
-            const int n0 = min(p.s0, nplanes);
-            for (int q = 0; q < n0; q++) {
-                mbar_expect_tx(bar0 + 8u * q, box0_bytes);
-                tma_load_3d(smem_u32(ring0 + (size_t)q * slot0_bytes), &p.map_io, c0_io, c1_io, xa + 1 + q, bar0 + 8u * q);
-            }
-        }
-        // the layer's time argument and coefficient come from the launch parameters or,
-        // in per-step (end-to-end) mode, from the descriptor the host uploaded for this step
+        // the layer's time argument and coefficient come from the launch parameters or, in per-step
+        // (end-to-end) mode, from the descriptor the host uploaded for this step
         const double arg_t = p.desc ? p.desc[0] : p.arg_t;
         const double c = cos(arg_t);
         s_bcast[0] = c;
@@ -256,143 +271,173 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) k_step(const __grid_constan
         s_bcast[2] = p.desc ? p.desc[1] : p.coef;
     }
     __syncthreads();
-    const double cosn = s_bcast[0];
-    const double rcos = s_bcast[1];
-    const double coef = s_bcast[2];
 
-    // ---- per-thread geometry
-    const int kk = k0 + 2 * lane;  // owned k of the first cell
-    const bool vk0 = kk <= p.hi2, vk1 = kk + 1 <= p.hi2;
-    bool vj[RJ];
-    double syq[RJ], rsyq[RJ];
-#pragma unroll
-    for (int q = 0; q < RJ; q++) {
-        const int j = j0 + warp * RJ + q;
-        vj[q] = j <= p.hi1;
-        syq[q] = vj[q] ? p.sy[j] : 0.0;
-        rsyq[q] = vj[q] ? p.rsy[j] : 0.0;
-    }
-    const double szk0 = vk0 ? p.sz[kk] : 0.0, szk1 = vk1 ? p.sz[kk + 1] : 0.0;
-    const double rsz0 = vk0 ? p.rsz[kk] : 0.0, rsz1 = vk1 ? p.rsz[kk + 1] : 0.0;
-    const bool zlo_face = (p.push_mask & 16u) && kk == 0;  // owned k == 0 is cell .x of lane 0 of z-tile 0
-    const bool zhi_face0 = (p.push_mask & 32u) && kk == p.Z - 1;
-    const bool zhi_face1 = (p.push_mask & 32u) && kk + 1 == p.Z - 1;
-
-    ErrAcc ea = {0.0, 0.0, 0.0, 0.0};
-
-    const int colc = 2 + 2 * lane;  // my first cell inside a halo-slot row
-    mbar_wait(bar1, 0);
-    if (p.s1 > 1) mbar_wait(bar1 + 8u, 0);
-
-    for (int t = 0; t < nplanes; t++) {
-        const int i = xa + t;  // owned x index of the centre plane
-        {
-            const int q = t + 2;
-            mbar_wait(bar1 + 8u * (q % p.s1), (uint32_t)((q / p.s1) & 1));
+    if (warp == ncw) {
+        // ================= producer warp: one lane feeds both rings with TMA =================
+        if (lane == 0) {
+            // Neighbours must have finished the previous layer: their ghost stores are complete (RAW)
+            // and they no longer read the ghosts this layer overwrites (WAR). Nothing of this CTA
+            // touches global memory before its first plane has arrived, i.e. after this wait.
+            const unsigned long long t0 = globaltimer_ns();
+            for (int f = 0; f < 6; f++) {
+                const uint32_t* fl = p.flag_in[f];
+                if (!fl) continue;
+                while (ld_acquire_sys(fl) < p.epoch_wait) {
+                    __nanosleep(64);
+                    if (globaltimer_ns() - t0 > p.timeout_ns) {
+                        atomicExch(&p.scratch[1], 1u);
+                        break;
+                    }
+                }
+            }
+            asm volatile("fence.proxy.async;" ::: "memory");
+            const uint32_t box1_bytes = (uint32_t)((p.ty + 2) * kW1 * 8);
+            const uint32_t box0_bytes = (uint32_t)(p.ty * kTZ * 8);
+            const int c0_src = p.oz + k0 - 2, c1_src = j0;  // storage row(j0) - 1 == j0
+            const int c0_io = p.oz + k0, c1_io = j0 + 1;
+            int s1i = 0, s0i = 0;
+            uint32_t ph1 = 1, ph0 = 1;  // parity of the "previous" phase: passes immediately on first use
+            for (int q = 0; q < nplanes + 2; q++) {
+                // source plane seq q = owned plane xa-1+q = storage plane xa+q
+                mbar_wait(empty1 + 8u * s1i, ph1);
+                mbar_expect_tx(full1 + 8u * s1i, box1_bytes);
+                tma_load_3d(ring1 + (uint32_t)s1i * slot1_bytes, &p.map_src, c0_src, c1_src, xa + q, full1 + 8u * s1i);
+                if (++s1i == p.s1) { s1i = 0; ph1 ^= 1; }
+                if (!FIRST && q >= 2) {
+                    // in-place plane of iteration q-2 = owned plane xa+q-2 = storage plane xa+q-1
+                    mbar_wait(empty0 + 8u * s0i, ph0);
+                    mbar_expect_tx(full0 + 8u * s0i, box0_bytes);
+                    tma_load_3d(ring0 + (uint32_t)s0i * slot0_bytes, &p.map_io, c0_io, c1_io, xa + q - 1, full0 + 8u * s0i);
+                    if (++s0i == p.s0) { s0i = 0; ph0 ^= 1; }
+                }
+            }
         }
-        if (!FIRST) mbar_wait(bar0 + 8u * (t % p.s0), (uint32_t)((t / p.s0) & 1));
-
-        const double* sm = reinterpret_cast<const double*>(ring1 + (size_t)(t % p.s1) * slot1_bytes);
-        const double* sc = reinterpret_cast<const double*>(ring1 + (size_t)((t + 1) % p.s1) * slot1_bytes);
-        const double* sp = reinterpret_cast<const double*>(ring1 + (size_t)((t + 2) % p.s1) * slot1_bytes);
-        const double* s0 = reinterpret_cast<const double*>(ring0 + (size_t)(FIRST ? 0 : (t % p.s0)) * slot0_bytes);
-
-        const bool ei = i >= p.elo0 && i <= p.ehi0;
-        const double cs = __dmul_rn(cosn, p.sx[i]);
-        const double rcs = __dmul_rn(rcos, p.rsx[i]);
-        const bool xlo_face = (p.push_mask & 1u) && i == p.send_x0;
-        const bool xhi_face = (p.push_mask & 2u) && i == p.send_x1;
-
-        const int r0 = warp * RJ;
-        double2 rowc[RJ + 2];
-#pragma unroll
-        for (int q = 0; q < RJ + 2; q++) rowc[q] = *reinterpret_cast<const double2*>(sc + (r0 + q) * W1 + colc);
-
+    } else {
+        // ================================ compute warps ================================
+        const double cosn = s_bcast[0], rcos = s_bcast[1], coef = s_bcast[2];
+        const int kk = k0 + 2 * lane;  // owned k of my first cell
+        const bool vk0 = kk <= p.hi2, vk1 = kk + 1 <= p.hi2;
+        const int jr = j0 + warp * RJ;  // owned j of my first row
+        bool vj[RJ], slow[RJ];
+        double syq[RJ], rsyq[RJ];
+        double* orow[RJ];
+        const bool zface = ((p.push_mask & 16u) && kk == 0) || ((p.push_mask & 32u) && (kk == p.Z - 1 || kk + 1 == p.Z - 1));
 #pragma unroll
         for (int q = 0; q < RJ; q++) {
-            const int r = r0 + q;
-            const double2 c = rowc[q + 1], ym = rowc[q], yp = rowc[q + 2];
-            const double zl = sc[(r + 1) * W1 + colc - 1];
-            const double zr = sc[(r + 1) * W1 + colc + 2];
-            const double2 xm = *reinterpret_cast<const double2*>(sm + (r + 1) * W1 + colc);
-            const double2 xp = *reinterpret_cast<const double2*>(sp + (r + 1) * W1 + colc);
-            double2 g0 = c;
-            if (!FIRST) g0 = *reinterpret_cast<const double2*>(s0 + r * p.tz + 2 * lane);
-
-            // exact expression order of the reference build
-            const double c2a = __dadd_rn(c.x, c.x), c2b = __dadd_rn(c.y, c.y);
-            const double sa_ = FIRST ? c.x : __dsub_rn(c2a, g0.x);
-            const double sb_ = FIRST ? c.y : __dsub_rn(c2b, g0.y);
-            const double lxa = div_const<DIV>(__dsub_rn(__dadd_rn(xp.x, xm.x), c2a), p.hx2, p.rx);
-            const double lxb = div_const<DIV>(__dsub_rn(__dadd_rn(xp.y, xm.y), c2b), p.hx2, p.rx);
-            const double lya = div_const<DIV>(__dsub_rn(__dadd_rn(yp.x, ym.x), c2a), p.hy2, p.ry);
-            const double lyb = div_const<DIV>(__dsub_rn(__dadd_rn(yp.y, ym.y), c2b), p.hy2, p.ry);
-            const double lza = div_const<DIV>(__dsub_rn(__dadd_rn(c.y, zl), c2a), p.hz2, p.rz);
-            const double lzb = div_const<DIV>(__dsub_rn(__dadd_rn(zr, c.x), c2b), p.hz2, p.rz);
-            const double ua = __fma_rn(coef, __dadd_rn(__dadd_rn(lxa, lya), lza), sa_);
-            const double ub = __fma_rn(coef, __dadd_rn(__dadd_rn(lxb, lyb), lzb), sb_);
-
-            const int j = j0 + r;
-            const bool v0 = vj[q] && vk0, v1 = vj[q] && vk1;
-            if (v0) {
-                double* o = p.out + (int64_t)(i + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
-                store_pair(o, ua, ub, true, v1);
-                if (p.push_mask) {
-                    if (xlo_face) store_pair(p.dst[0] + j * p.sa[0] + kk * p.sb[0], ua, ub, true, v1 && p.sb[0] == 1);
-                    if (xlo_face && v1 && p.sb[0] != 1) p.dst[0][j * p.sa[0] + (kk + 1) * p.sb[0]] = ub;
-                    if (xhi_face) store_pair(p.dst[1] + j * p.sa[1] + kk * p.sb[1], ua, ub, true, v1 && p.sb[1] == 1);
-                    if (xhi_face && v1 && p.sb[1] != 1) p.dst[1][j * p.sa[1] + (kk + 1) * p.sb[1]] = ub;
-                    if ((p.push_mask & 4u) && j == 0) {
-                        store_pair(p.dst[2] + i * p.sa[2] + kk * p.sb[2], ua, ub, true, v1 && p.sb[2] == 1);
-                        if (v1 && p.sb[2] != 1) p.dst[2][i * p.sa[2] + (kk + 1) * p.sb[2]] = ub;
-                    }
-                    if ((p.push_mask & 8u) && j == p.Y - 1) {
-                        store_pair(p.dst[3] + i * p.sa[3] + kk * p.sb[3], ua, ub, true, v1 && p.sb[3] == 1);
-                        if (v1 && p.sb[3] != 1) p.dst[3][i * p.sa[3] + (kk + 1) * p.sb[3]] = ub;
-                    }
-                    if (zlo_face) p.dst[4][i * p.sa[4] + j * p.sb[4]] = ua;
-                    if (zhi_face0) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ua;
-                    if (zhi_face1 && v1) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ub;
-                }
-                if (ei) {
-                    const double fxy = __dmul_rn(cs, syq[q]);
-                    const double rxy = __dmul_rn(rcs, rsyq[q]);
-                    err_cell(ea, ua, __dmul_rn(fxy, szk0), rxy, rsz0);
-                    if (v1) err_cell(ea, ub, __dmul_rn(fxy, szk1), rxy, rsz1);
-                }
-            }
+            const int j = jr + q;
+            vj[q] = j <= p.hi1 && vk0;
+            syq[q] = vj[q] ? p.sy[j] : 0.0;
+            rsyq[q] = vj[q] ? p.rsy[j] : 0.0;
+            slow[q] = vj[q] && (zface || ((p.push_mask & 4u) && j == 0) || ((p.push_mask & 8u) && j == p.Y - 1));
+            orow[q] = p.out + (int64_t)(xa + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
         }
+        const double szk0 = vk0 ? p.sz[kk] : 0.0, szk1 = vk1 ? p.sz[kk + 1] : 0.0;
+        const double rsz0 = vk0 ? p.rsz[kk] : 0.0, rsz1 = vk1 ? p.rsz[kk + 1] : 0.0;
+        const double hx2 = p.hx2, hy2 = p.hy2, hz2 = p.hz2, rx = p.rx, ry = p.ry, rz = p.rz;
+        const int64_t ps = p.ps;
+        const bool xpush = (p.push_mask & 3u) != 0;
+        ErrAcc ea = {0.0, 0.0, 0.0, 0.0};
 
-        __syncthreads();  // everyone is done with plane i-1 (ring1 slot t) and in-place plane i (ring0 slot t)
-        if (tid == 0) {
-            const int q1 = t + p.s1;
-            if (q1 < nplanes + 2) {
-                const uint32_t b = bar1 + 8u * (t % p.s1);
-                mbar_expect_tx(b, box1_bytes);
-                tma_load_3d(smem_u32(ring1 + (size_t)(t % p.s1) * slot1_bytes), &p.map_src, c0_src, c1_src, xa + q1, b);
+        // byte offset of (my first row's upper halo row, my first cell) inside a halo slot / core slot
+        const uint32_t toff1 = (uint32_t)(((warp * RJ) * kW1 + 2 + 2 * lane) * 8);
+        const uint32_t toff0 = (uint32_t)(((warp * RJ) * kTZ + 2 * lane) * 8);
+        const uint32_t ring1_end = ring1 + (uint32_t)p.s1 * slot1_bytes;
+        const uint32_t ring0_end = ring0 + (uint32_t)p.s0 * slot0_bytes;
+
+        // slots of planes i-1, i, i+1 and the barrier walking with plane i+1
+        uint32_t am = ring1, ac = ring1 + slot1_bytes, ap = ring1 + 2 * slot1_bytes;
+        uint32_t bfp = full1 + 16u, bem = empty1;  // full barrier of ap's slot, empty barrier of am's slot
+        uint32_t php = 0;
+        uint32_t a0 = ring0, bf0 = full0, be0 = empty0, ph0 = 0;
+        const uint32_t empty1_end = empty1 + 8u * (uint32_t)p.s1;
+        mbar_wait(full1, 0);
+        mbar_wait(full1 + 8u, 0);
+
+        for (int t = 0; t < nplanes; t++) {
+            const int i = xa + t;  // owned x index of the centre plane
+            mbar_wait(bfp, php);
+            if (!FIRST) mbar_wait(bf0, ph0);
+
+            const bool ei = i >= p.elo0 && i <= p.ehi0;
+            const double cs = __dmul_rn(cosn, __ldg(p.sx + i));
+            const double rcs = __dmul_rn(rcos, __ldg(p.rsx + i));
+            const bool pslow = xpush && (i == p.send_x0 || i == p.send_x1);
+
+            double2 rowc[RJ + 2];
+#pragma unroll
+            for (int q = 0; q < RJ + 2; q++) rowc[q] = lds2(ac + toff1 + (uint32_t)(q * kW1 * 8));
+
+#pragma unroll
+            for (int q = 0; q < RJ; q++) {
+                const uint32_t rc = toff1 + (uint32_t)((q + 1) * kW1 * 8);
+                const double2 c = rowc[q + 1], ym = rowc[q], yp = rowc[q + 2];
+                const double zl = lds1(ac + rc - 8u);
+                const double zr = lds1(ac + rc + 16u);
+                const double2 xm = lds2(am + rc);
+                const double2 xp = lds2(ap + rc);
+                double2 g0 = c;
+                if (!FIRST) g0 = lds2(a0 + toff0 + (uint32_t)(q * kTZ * 8));
+
+                // exact expression order of the reference build
+                const double c2a = __dadd_rn(c.x, c.x), c2b = __dadd_rn(c.y, c.y);
+                const double sa_ = FIRST ? c.x : __dsub_rn(c2a, g0.x);
+                const double sb_ = FIRST ? c.y : __dsub_rn(c2b, g0.y);
+                const double lxa = div_const<DIV>(__dsub_rn(__dadd_rn(xp.x, xm.x), c2a), hx2, rx);
+                const double lxb = div_const<DIV>(__dsub_rn(__dadd_rn(xp.y, xm.y), c2b), hx2, rx);
+                const double lya = div_const<DIV>(__dsub_rn(__dadd_rn(yp.x, ym.x), c2a), hy2, ry);
+                const double lyb = div_const<DIV>(__dsub_rn(__dadd_rn(yp.y, ym.y), c2b), hy2, ry);
+                const double lza = div_const<DIV>(__dsub_rn(__dadd_rn(c.y, zl), c2a), hz2, rz);
+                const double lzb = div_const<DIV>(__dsub_rn(__dadd_rn(zr, c.x), c2b), hz2, rz);
+                const double ua = __fma_rn(coef, __dadd_rn(__dadd_rn(lxa, lya), lza), sa_);
+                const double ub = __fma_rn(coef, __dadd_rn(__dadd_rn(lxb, lyb), lzb), sb_);
+
+                if (vj[q]) {
+                    if (vk1) *reinterpret_cast<double2*>(orow[q]) = make_double2(ua, ub);
+                    else *orow[q] = ua;
+                    if (slow[q] || pslow) push_row(p, i, jr + q, kk, ua, ub, vk1);
+                    if (ei) {
+                        const double fxy = __dmul_rn(cs, syq[q]);
+                        const double rxy = __dmul_rn(rcs, rsyq[q]);
+                        if (vk1) err_row<true>(ea, ua, ub, fxy, rxy, szk0, szk1, rsz0, rsz1);
+                        else err_row<false>(ea, ua, ub, fxy, rxy, szk0, szk1, rsz0, rsz1);
+                    }
+                }
+                orow[q] += ps;
             }
+
+            // this warp is done with plane i-1 (source ring) and in-place plane i
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(bem);
+                if (!FIRST) mbar_arrive(be0);
+            }
+            // rotate: (i-1, i, i+1) <- (i, i+1, i+2)
+            am = ac;
+            ac = ap;
+            ap += slot1_bytes;
+            bfp += 8u;
+            if (ap == ring1_end) { ap = ring1; bfp = full1; php ^= 1; }
+            bem += 8u;
+            if (bem == empty1_end) bem = empty1;
             if (!FIRST) {
-                const int q0 = t + p.s0;
-                if (q0 < nplanes) {
-                    const uint32_t b = bar0 + 8u * (t % p.s0);
-                    mbar_expect_tx(b, box0_bytes);
-                    tma_load_3d(smem_u32(ring0 + (size_t)(t % p.s0) * slot0_bytes), &p.map_io, c0_io, c1_io, xa + 1 + q0, b);
-                }
+                a0 += slot0_bytes;
+                bf0 += 8u;
+                be0 += 8u;
+                if (a0 == ring0_end) { a0 = ring0; bf0 = full0; be0 = empty0; ph0 ^= 1; }
             }
         }
-    }
 
-    // ---- error maxima: warp -> CTA -> device table
-    const double wa = warp_max(ea.mabs), wr = warp_max(ea.mrel);
-    if (lane == 0) {
-        s_red[warp][0] = wa;
-        s_red[warp][1] = wr;
+        // ---- error maxima: warp -> CTA
+        const double wa = warp_max(ea.mabs), wr = warp_max(ea.mrel);
+        if (lane == 0) {
+            s_red[warp][0] = wa;
+            s_red[warp][1] = wr;
+        }
     }
     __syncthreads();  // also orders every thread's global / peer stores before thread 0's fence
     if (tid == 0) {
         double a = 0.0, r = 0.0;
-        const int nw = blockDim.x >> 5;
-        for (int w = 0; w < nw; w++) {
+        for (int w = 0; w < ncw; w++) {
             a = fmax(a, s_red[w][0]);
             r = fmax(r, s_red[w][1]);
         }
@@ -637,7 +682,7 @@ int choose_div_mode(const wave3d_problem* p) {
 int plan_smem_bytes(int ty, int tz, int s1, int s0) {
     const int slot1 = ((ty + 2) * (tz + 4) * 8 + 127) & ~127;
     const int slot0 = (ty * tz * 8 + 127) & ~127;
-    return 128 + s1 * slot1 + s0 * slot0 + 8 * (s1 + s0) + 64;
+    return 128 + s1 * slot1 + s0 * slot0 + 16 * (s1 + s0) + 64;
 }
 
 typedef void (*StepKernel)(const StepParams);
@@ -690,7 +735,7 @@ int step_occupancy(int rj, int warps, int smem_bytes) {
         return 0;
     }
     int nb = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)k, warps * 32, smem_bytes) != cudaSuccess) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)k, (warps + 1) * 32, smem_bytes) != cudaSuccess) {
         cudaGetLastError();
         return 0;
     }
@@ -752,7 +797,7 @@ int launch_step(const StepLaunch& a) {
     const int smem = plan_smem_bytes(pl->ty, pl->tz, pl->s1, a.first ? 0 : pl->s0);
     if (ensure_smem_attr((const void*)k, smem)) return -1;
     const int grid = pl->nty * pl->ntz * pl->nchunks;
-    k<<<grid, pl->warps * 32, smem, a.stream>>>(p);
+    k<<<grid, (pl->warps + 1) * 32, smem, a.stream>>>(p);  // + the TMA producer warp
     W3D_TRY(cudaGetLastError());
     return 0;
 }

@@ -288,7 +288,7 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
     int nov = 0;
     if (const char* e = getenv("WAVE3D_TILE")) nov = sscanf(e, "%d,%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3], &ov[4]);
     for (int rj = 1; rj <= 4; rj *= 2) {
-        for (int warps = 2; warps <= 16; warps++) {
+        for (int warps = 2; warps <= 11; warps++) {
             const int ty = rj * warps;
             if (ty > 64) continue;
             if (nov >= 2 && (ty != ov[0] || rj != ov[1])) continue;
@@ -303,7 +303,7 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
             int occ = 0;
             if (have_gpu) occ = step_occupancy(rj, warps, smem);
             if (occ <= 0) {
-                occ = std::min(232448 / (smem + 1024), std::min(64 / warps, 21 / warps));
+                occ = std::min(232448 / (smem + 1024), std::min(64 / (warps + 1), 18 / (warps + 1)));
                 if (occ < 1) occ = 1;
             }
             const int nty = (ny + ty - 1) / ty;

@@ -16,7 +16,7 @@ def test_plan_is_feasible(N, nranks, dims):
     for r in {0, nranks - 1}:
         box = dec.box(r)
         pl = K.plan_for(box, 148)
-        assert pl.tz == 64 and pl.rj in (1, 2, 4) and 2 <= pl.warps <= 16 and pl.ty == pl.rj * pl.warps
+        assert pl.tz == 64 and pl.rj in (1, 2, 4) and 2 <= pl.warps <= 11 and pl.ty == pl.rj * pl.warps
         assert pl.nty * pl.ty >= box.hi[1] - box.lo[1] + 1
         assert pl.ntz * pl.tz >= box.hi[2] - box.lo[2] + 1
         assert 1 <= pl.nchunks <= max(1, box.n[0] // 8)
