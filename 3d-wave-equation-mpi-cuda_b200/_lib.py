@@ -132,6 +132,7 @@ def _sig(lib):
         "wave3d_cuda_push_faces": (i32, [B, L, vp, C.POINTER(Peers), C.c_uint32, vp]),
         "wave3d_cuda_field_error_scratch_words": (i64, [B]),
         "wave3d_cuda_field_error": (i32, [P, B, L, C.POINTER(vp), vp, i32, vp, vp, vp]),
+        "wave3d_cuda_field_error_static": (i32, [P, B, L, C.POINTER(vp), vp, i32, i32, vp, vp]),
         "wave3d_solver_opts_default": (None, [C.POINTER(SolverOpts)]),
         "wave3d_solver_create": (vp, [P, C.POINTER(SolverOpts), cs, C.c_size_t]),
         "wave3d_solver_destroy": (None, [vp]),

@@ -948,3 +948,89 @@ int wave3d_cuda_step(const wave3d_problem* p, const wave3d_box* b, const wave3d_
 }
 
 }  // extern "C"
+
+namespace w3d {
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free flavour of the stand-alone error evaluation.
+//
+// wave3d_cuda_field_error() needs a few KB of scratch that its caller has to cudaMalloc (or get
+// from torch). Some users of this library are not in a position to allocate device memory at the
+// moment they want an error figure: an in-situ monitor that is attached to a production run whose
+// job script has already handed every free byte of HBM to the solver or to a pooling allocator
+// (a cudaMalloc there can simply fail); a real-time / latency-critical loop that must not take
+// the device-wide synchronisation cudaMalloc and cudaFree imply; a plug-in that runs inside a
+// host callback or a foreign framework's "no allocation" region. For them the scratch lives in
+// the library image itself: one file-scope __device__ array per loaded module, i.e. every GPU
+// that loads libwave3d keeps these ~19 KB until the process exits, whether or not this entry
+// point is ever used.
+//
+// The array is shared by all calls on a device and still holds whatever the previous call left
+// there, so every call first clears the one word the kernel needs at zero (the CTA ticket) in
+// stream order. Two calls whose kernels overlap on the same GPU (different streams, or threads
+// racing) would share ticket and partial maxima and corrupt each other — callers serialise them.
+//
+// A host function cannot use the array's name as a pointer: on the host that name is only a
+// handle for the runtime. The device address is looked up with cudaGetSymbolAddress, once per
+// device, by the first call made while that device is current; that first call may load the
+// module and should therefore be made before any stream capture is started on the device.
+constexpr int kStaticErrMaxBlocks = 1184;                      // 8 resident CTAs x 148 SMs
+constexpr int kStaticErrWords = 2 + 2 * kStaticErrMaxBlocks;   // ticket + pad, (abs, rel) per CTA
+static __device__ __align__(256) unsigned long long g_static_err_scratch[kStaticErrWords];
+
+static int static_err_scratch_ptr(unsigned long long** out) {
+    static std::mutex mu;
+    static unsigned long long* per_device[64] = {nullptr};
+    int dev = -1;
+    W3D_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_last_error("wave3d_cuda_field_error_static: device index " + std::to_string(dev) + " not supported (max 63)");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!per_device[dev]) {
+        unsigned long long* ptr = nullptr;
+        W3D_TRY(cudaGetSymbolAddress((void**)&ptr, g_static_err_scratch));
+        if (!ptr) {
+            set_last_error("wave3d_cuda_field_error_static: cudaGetSymbolAddress returned a null address");
+            return -1;
+        }
+        per_device[dev] = ptr;
+    }
+    *out = per_device[dev];
+    return 0;
+}
+
+}  // namespace w3d
+
+extern "C" int wave3d_cuda_field_error_static(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l,
+                                              const double* const tabs[6], const double* u, int n, int blocks,
+                                              double* out, void* stream) {
+    using namespace w3d;
+    FErrParams g;
+    for (int a = 0; a < 3; a++) {
+        g.lo[a] = b->elo[a];
+        g.hi[a] = b->ehi[a];
+    }
+    g.oz = l->oz; g.ps = l->plane_stride; g.pitch = l->pitch;
+    g.arg_t = std::fma(p->a_t * (double)n, p->tau, p->pi + p->pi);
+    const int64_t rows = (int64_t)(g.hi[0] - g.lo[0] + 1) * (g.hi[1] - g.lo[1] + 1);
+    int64_t nb = blocks > 0 ? blocks : (rows + 7) / 8;   // same rule as wave3d_cuda_field_error ...
+    if (blocks <= 0 && nb > kStaticErrMaxBlocks) nb = kStaticErrMaxBlocks;  // ... including its cap
+    if (nb < 1) nb = 1;
+    if (nb > kStaticErrMaxBlocks) {
+        set_last_error("wave3d_cuda_field_error_static: " + std::to_string((long long)nb) +
+                       " CTAs requested but the built-in scratch holds partial maxima for at most " +
+                       std::to_string(kStaticErrMaxBlocks) + " (" + std::to_string(kStaticErrWords * 8) +
+                       " bytes); use fewer blocks or wave3d_cuda_field_error with caller-allocated scratch");
+        return -1;
+    }
+    unsigned long long* scratch = nullptr;
+    if (static_err_scratch_ptr(&scratch)) return -1;
+    // the previous call's partial maxima may stay (every CTA overwrites its own slot before the
+    // last CTA reads them); the ticket must start at zero
+    W3D_TRY(cudaMemsetAsync(scratch, 0, 16, (cudaStream_t)stream));
+    k_field_error<<<(int)nb, 256, 0, (cudaStream_t)stream>>>(g, u, tabs[0], tabs[1], tabs[2], scratch, out);
+    W3D_TRY(cudaGetLastError());
+    return 0;
+}

@@ -254,6 +254,21 @@ int wave3d_cuda_field_error(const wave3d_problem* p, const wave3d_box* b, const 
                             const double* const tabs[6], const double* u, int n, uint64_t* scratch, double* out,
                             void* stream);
 
+/* Same evaluation without any allocation, for callers that cannot obtain device memory when they
+ * need the figure (a monitor attached to a run that has reserved all HBM, a latency-critical loop
+ * that must avoid the device-wide synchronisation of cudaMalloc/cudaFree, code inside a foreign
+ * framework's no-allocation region). This entry point has no counterpart in the reference.
+ * The scratch is a ~19 KB __device__ array inside the library, present on every GPU that loads it
+ * until the process exits. `blocks` = number of CTAs (<= 0: the rule of wave3d_cuda_field_error);
+ * more than WAVE3D_FIELD_ERROR_STATIC_MAX_BLOCKS is refused with an error. All calls on a device
+ * share that array: calls whose kernels may overlap on one GPU must be serialised by the caller.
+ * The first call on each device looks up the array's device address (it may load the module), so
+ * make it before starting a stream capture on that device. out[0]=max abs, out[1]=max rel. */
+#define WAVE3D_FIELD_ERROR_STATIC_MAX_BLOCKS 1184
+int wave3d_cuda_field_error_static(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l,
+                                   const double* const tabs[6], const double* u, int n, int blocks, double* out,
+                                   void* stream);
+
 /* ------------------------------------------------------------------ solver -- */
 /* A solver owns the ranks that live in this process: all of them (native CLI,
  * single process driving 1..8 GPUs, or several ranks time-sharing one GPU for
