@@ -30,7 +30,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=512, help="grid intervals per axis (BASELINE config 3: 512)")
+    ap.add_argument("--grid", dest="n", type=int, default=512, help="grid intervals per axis (BASELINE config 3: 512)")
     ap.add_argument("--length", default="1", help="box length: a number or 'pi'")
     ap.add_argument("--dims", default=None, help="force the process grid, e.g. 8x1x1")
     ap.add_argument("--transport", default="auto", choices=["auto", "peer", "staged"])

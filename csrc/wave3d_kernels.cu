@@ -209,22 +209,19 @@ __device__ __forceinline__ void store_pair(double* p, double a, double b, bool t
 }
 
 // Face cells are stored a second time, straight into the neighbour's ghost cells (peer memory).
-__device__ __noinline__ void push_row(const StepParams& p, int i, int j, int kk, double ua, double ub, bool two) {
+// x faces: whole planes, hit on at most two planes per rank -> out of line; y and z faces are
+// stored inline in the march through per-thread pointers.
+__device__ __noinline__ void push_row_x(const StepParams& p, int i, int j, int kk, double ua, double ub, bool two) {
     if ((p.push_mask & 1u) && i == p.send_x0) store_pair(p.dst[0] + j * p.sa[0] + kk, ua, ub, two);
     if ((p.push_mask & 2u) && i == p.send_x1) store_pair(p.dst[1] + j * p.sa[1] + kk, ua, ub, two);
-    if ((p.push_mask & 4u) && j == 0) store_pair(p.dst[2] + i * p.sa[2] + kk, ua, ub, two);
-    if ((p.push_mask & 8u) && j == p.Y - 1) store_pair(p.dst[3] + i * p.sa[3] + kk, ua, ub, two);
-    if ((p.push_mask & 16u) && kk == 0) p.dst[4][i * p.sa[4] + j * p.sb[4]] = ua;
-    if ((p.push_mask & 32u) && kk == p.Z - 1) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ua;
-    if ((p.push_mask & 32u) && two && kk + 1 == p.Z - 1) p.dst[5][i * p.sa[5] + j * p.sb[5]] = ub;
 }
 
-constexpr int kMaxWarps = 11;   // compute warps per CTA (one more warp is the TMA producer): 384 threads max
+constexpr int kMaxWarps = 7;    // compute warps per CTA (one more warp is the TMA producer): 256 threads, 2 CTAs per SM
 constexpr int kTZ = 64;         // tile width in z: one warp row = 32 lanes x 2 cells
 constexpr int kW1 = kTZ + 4;    // halo slot row length in doubles (2 halo columns each side keep 16-byte alignment)
 
 template <int RJ, bool FIRST, int DIV>
-__global__ void __launch_bounds__((kMaxWarps + 1) * 32, 1) k_step(const __grid_constant__ StepParams p) {
+__global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_constant__ StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_bcast[3];
     __shared__ double s_red[kMaxWarps][2];
@@ -239,16 +236,11 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 1) k_step(const __grid_c
     const uint32_t full1 = bars, empty1 = full1 + 8u * (uint32_t)p.s1;
     const uint32_t full0 = empty1 + 8u * (uint32_t)p.s1, empty0 = full0 + 8u * (uint32_t)p.s0;
 
-    // ---- work item: (z tile, y tile, x chunk)
-    const int bid = blockIdx.x;
-    const int tzi = bid % p.ntz;
-    const int tyi = (bid / p.ntz) % p.nty;
-    const int cxi = bid / (p.ntz * p.nty);
-    const int j0 = p.lo1 + tyi * p.ty;
-    const int k0 = p.lo2 + tzi * kTZ;
-    const int xa = (int)(((int64_t)p.X * cxi) / p.nchunks);
-    const int xb = (int)(((int64_t)p.X * (cxi + 1)) / p.nchunks);
-    const int nplanes = xb - xa;
+    // ---- persistent, balanced work split: the (tile, x-plane) units of this rank are dealt out in
+    // equal contiguous ranges; a CTA marches its range tile column by tile column
+    const int64_t units = (int64_t)p.nty * p.ntz * p.X;
+    int64_t u_beg = units * blockIdx.x / gridDim.x;
+    const int64_t u_end = units * (blockIdx.x + 1) / gridDim.x;
 
     if (tid == 0) {
         for (int s = 0; s < p.s1; s++) {
@@ -283,7 +275,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 1) k_step(const __grid_c
                 const uint32_t* fl = p.flag_in[f];
                 if (!fl) continue;
                 while (ld_acquire_sys(fl) < p.epoch_wait) {
-                    __nanosleep(64);
+                    __nanosleep(32);
                     if (globaltimer_ns() - t0 > p.timeout_ns) {
                         atomicExch(&p.scratch[1], 1u);
                         break;
@@ -293,138 +285,204 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 1) k_step(const __grid_c
             asm volatile("fence.proxy.async;" ::: "memory");
             const uint32_t box1_bytes = (uint32_t)((p.ty + 2) * kW1 * 8);
             const uint32_t box0_bytes = (uint32_t)(p.ty * kTZ * 8);
-            const int c0_src = p.oz + k0 - 2, c1_src = j0;  // storage row(j0) - 1 == j0
-            const int c0_io = p.oz + k0, c1_io = j0 + 1;
             int s1i = 0, s0i = 0;
             uint32_t ph1 = 1, ph0 = 1;  // parity of the "previous" phase: passes immediately on first use
-            for (int q = 0; q < nplanes + 2; q++) {
-                // source plane seq q = owned plane xa-1+q = storage plane xa+q
-                mbar_wait(empty1 + 8u * s1i, ph1);
-                mbar_expect_tx(full1 + 8u * s1i, box1_bytes);
-                tma_load_3d(ring1 + (uint32_t)s1i * slot1_bytes, &p.map_src, c0_src, c1_src, xa + q, full1 + 8u * s1i);
-                if (++s1i == p.s1) { s1i = 0; ph1 ^= 1; }
-                if (!FIRST && q >= 2) {
-                    // in-place plane of iteration q-2 = owned plane xa+q-2 = storage plane xa+q-1
-                    mbar_wait(empty0 + 8u * s0i, ph0);
-                    mbar_expect_tx(full0 + 8u * s0i, box0_bytes);
-                    tma_load_3d(ring0 + (uint32_t)s0i * slot0_bytes, &p.map_io, c0_io, c1_io, xa + q - 1, full0 + 8u * s0i);
-                    if (++s0i == p.s0) { s0i = 0; ph0 ^= 1; }
+            while (u_beg < u_end) {
+                const int tile = (int)(u_beg / p.X);
+                const int xa = (int)(u_beg - (int64_t)tile * p.X);
+                const int nplanes = (int)min((int64_t)(p.X - xa), u_end - u_beg);
+                const int j0 = p.lo1 + (tile / p.ntz) * p.ty;
+                const int k0 = p.lo2 + (tile % p.ntz) * kTZ;
+                const int c0_src = p.oz + k0 - 2, c1_src = j0;  // storage row(j0) - 1 == j0
+                const int c0_io = p.oz + k0, c1_io = j0 + 1;
+                for (int q = 0; q < nplanes + 2; q++) {
+                    // source plane seq q = owned plane xa-1+q = storage plane xa+q
+                    mbar_wait(empty1 + 8u * s1i, ph1);
+                    mbar_expect_tx(full1 + 8u * s1i, box1_bytes);
+                    tma_load_3d(ring1 + (uint32_t)s1i * slot1_bytes, &p.map_src, c0_src, c1_src, xa + q, full1 + 8u * s1i);
+                    if (++s1i == p.s1) { s1i = 0; ph1 ^= 1; }
+                    if (!FIRST && q >= 2) {
+                        // in-place plane of iteration q-2 = owned plane xa+q-2 = storage plane xa+q-1
+                        mbar_wait(empty0 + 8u * s0i, ph0);
+                        mbar_expect_tx(full0 + 8u * s0i, box0_bytes);
+                        tma_load_3d(ring0 + (uint32_t)s0i * slot0_bytes, &p.map_io, c0_io, c1_io, xa + q - 1, full0 + 8u * s0i);
+                        if (++s0i == p.s0) { s0i = 0; ph0 ^= 1; }
+                    }
                 }
+                u_beg += nplanes;
             }
         }
     } else {
         // ================================ compute warps ================================
         const double cosn = s_bcast[0], rcos = s_bcast[1], coef = s_bcast[2];
-        const int kk = k0 + 2 * lane;  // owned k of my first cell
-        const bool vk0 = kk <= p.hi2, vk1 = kk + 1 <= p.hi2;
-        const int jr = j0 + warp * RJ;  // owned j of my first row
-        bool vj[RJ], slow[RJ];
-        double syq[RJ], rsyq[RJ];
-        double* orow[RJ];
-        const bool zface = ((p.push_mask & 16u) && kk == 0) || ((p.push_mask & 32u) && (kk == p.Z - 1 || kk + 1 == p.Z - 1));
-#pragma unroll
-        for (int q = 0; q < RJ; q++) {
-            const int j = jr + q;
-            vj[q] = j <= p.hi1 && vk0;
-            syq[q] = vj[q] ? p.sy[j] : 0.0;
-            rsyq[q] = vj[q] ? p.rsy[j] : 0.0;
-            slow[q] = vj[q] && (zface || ((p.push_mask & 4u) && j == 0) || ((p.push_mask & 8u) && j == p.Y - 1));
-            orow[q] = p.out + (int64_t)(xa + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
-        }
-        const double szk0 = vk0 ? p.sz[kk] : 0.0, szk1 = vk1 ? p.sz[kk + 1] : 0.0;
-        const double rsz0 = vk0 ? p.rsz[kk] : 0.0, rsz1 = vk1 ? p.rsz[kk + 1] : 0.0;
         const double hx2 = p.hx2, hy2 = p.hy2, hz2 = p.hz2, rx = p.rx, ry = p.ry, rz = p.rz;
         const int64_t ps = p.ps;
         const bool xpush = (p.push_mask & 3u) != 0;
         ErrAcc ea = {0.0, 0.0, 0.0, 0.0};
-
         // byte offset of (my first row's upper halo row, my first cell) inside a halo slot / core slot
         const uint32_t toff1 = (uint32_t)(((warp * RJ) * kW1 + 2 + 2 * lane) * 8);
         const uint32_t toff0 = (uint32_t)(((warp * RJ) * kTZ + 2 * lane) * 8);
-        const uint32_t ring1_end = ring1 + (uint32_t)p.s1 * slot1_bytes;
-        const uint32_t ring0_end = ring0 + (uint32_t)p.s0 * slot0_bytes;
+        // ring cursors: F = next source plane to arrive, B = oldest source plane still held, F0 = in-place ring
+        int fi = 0, bi = 0, f0i = 0;
+        uint32_t fph = 0, f0ph = 0;
 
-        // slots of planes i-1, i, i+1 and the barrier walking with plane i+1
-        uint32_t am = ring1, ac = ring1 + slot1_bytes, ap = ring1 + 2 * slot1_bytes;
-        uint32_t bfp = full1 + 16u, bem = empty1;  // full barrier of ap's slot, empty barrier of am's slot
-        uint32_t php = 0;
-        uint32_t a0 = ring0, bf0 = full0, be0 = empty0, ph0 = 0;
-        const uint32_t empty1_end = empty1 + 8u * (uint32_t)p.s1;
-        mbar_wait(full1, 0);
-        mbar_wait(full1 + 8u, 0);
+        while (u_beg < u_end) {
+            const int tile = (int)(u_beg / p.X);
+            const int xa = (int)(u_beg - (int64_t)tile * p.X);
+            const int nplanes = (int)min((int64_t)(p.X - xa), u_end - u_beg);
+            u_beg += nplanes;
+            const int j0 = p.lo1 + (tile / p.ntz) * p.ty;
+            const int k0 = p.lo2 + (tile % p.ntz) * kTZ;
 
-        for (int t = 0; t < nplanes; t++) {
-            const int i = xa + t;  // owned x index of the centre plane
-            mbar_wait(bfp, php);
-            if (!FIRST) mbar_wait(bf0, ph0);
-
-            const bool ei = i >= p.elo0 && i <= p.ehi0;
-            const double cs = __dmul_rn(cosn, __ldg(p.sx + i));
-            const double rcs = __dmul_rn(rcos, __ldg(p.rsx + i));
-            const bool pslow = xpush && (i == p.send_x0 || i == p.send_x1);
-
-            double2 rowc[RJ + 2];
-#pragma unroll
-            for (int q = 0; q < RJ + 2; q++) rowc[q] = lds2(ac + toff1 + (uint32_t)(q * kW1 * 8));
-
+            const int kk = k0 + 2 * lane;  // owned k of my first cell
+            const bool vk0 = kk <= p.hi2, vk1 = kk + 1 <= p.hi2;
+            const int jr = j0 + warp * RJ;  // owned j of my first row
+            bool vj[RJ];
+            double syq[RJ], rsyq[RJ];
+            double* orow[RJ];
+            // y faces: at most one of my rows is the rank's first / last owned row
+            int yq = -1;
+            double* yptr = nullptr;
+            int64_t ystep = 0;
+            // z faces: my first cell is the z- or z+ face column, or my second cell is the z+ one
+            double* zpa = nullptr;  // receives ua (row q at zpa + q * zsb)
+            double* zpb = nullptr;  // receives ub
+            int64_t zsb = 0, zstep = 0;
+            if ((p.push_mask & 16u) && kk == 0) {
+                zpa = p.dst[4] + xa * p.sa[4] + jr * p.sb[4];
+                zsb = p.sb[4];
+                zstep = p.sa[4];
+            }
+            if (p.push_mask & 32u) {
+                if (kk == p.Z - 1) {
+                    zpa = p.dst[5] + xa * p.sa[5] + jr * p.sb[5];
+                    zsb = p.sb[5];
+                    zstep = p.sa[5];
+                } else if (kk + 1 == p.Z - 1) {
+                    zpb = p.dst[5] + xa * p.sa[5] + jr * p.sb[5];
+                    zsb = p.sb[5];
+                    zstep = p.sa[5];
+                }
+            }
 #pragma unroll
             for (int q = 0; q < RJ; q++) {
-                const uint32_t rc = toff1 + (uint32_t)((q + 1) * kW1 * 8);
-                const double2 c = rowc[q + 1], ym = rowc[q], yp = rowc[q + 2];
-                const double zl = lds1(ac + rc - 8u);
-                const double zr = lds1(ac + rc + 16u);
-                const double2 xm = lds2(am + rc);
-                const double2 xp = lds2(ap + rc);
-                double2 g0 = c;
-                if (!FIRST) g0 = lds2(a0 + toff0 + (uint32_t)(q * kTZ * 8));
-
-                // exact expression order of the reference build
-                const double c2a = __dadd_rn(c.x, c.x), c2b = __dadd_rn(c.y, c.y);
-                const double sa_ = FIRST ? c.x : __dsub_rn(c2a, g0.x);
-                const double sb_ = FIRST ? c.y : __dsub_rn(c2b, g0.y);
-                const double lxa = div_const<DIV>(__dsub_rn(__dadd_rn(xp.x, xm.x), c2a), hx2, rx);
-                const double lxb = div_const<DIV>(__dsub_rn(__dadd_rn(xp.y, xm.y), c2b), hx2, rx);
-                const double lya = div_const<DIV>(__dsub_rn(__dadd_rn(yp.x, ym.x), c2a), hy2, ry);
-                const double lyb = div_const<DIV>(__dsub_rn(__dadd_rn(yp.y, ym.y), c2b), hy2, ry);
-                const double lza = div_const<DIV>(__dsub_rn(__dadd_rn(c.y, zl), c2a), hz2, rz);
-                const double lzb = div_const<DIV>(__dsub_rn(__dadd_rn(zr, c.x), c2b), hz2, rz);
-                const double ua = __fma_rn(coef, __dadd_rn(__dadd_rn(lxa, lya), lza), sa_);
-                const double ub = __fma_rn(coef, __dadd_rn(__dadd_rn(lxb, lyb), lzb), sb_);
-
-                if (vj[q]) {
-                    if (vk1) *reinterpret_cast<double2*>(orow[q]) = make_double2(ua, ub);
-                    else *orow[q] = ua;
-                    if (slow[q] || pslow) push_row(p, i, jr + q, kk, ua, ub, vk1);
-                    if (ei) {
-                        const double fxy = __dmul_rn(cs, syq[q]);
-                        const double rxy = __dmul_rn(rcs, rsyq[q]);
-                        if (vk1) err_row<true>(ea, ua, ub, fxy, rxy, szk0, szk1, rsz0, rsz1);
-                        else err_row<false>(ea, ua, ub, fxy, rxy, szk0, szk1, rsz0, rsz1);
-                    }
+                const int j = jr + q;
+                vj[q] = j <= p.hi1 && vk0;
+                syq[q] = vj[q] ? p.sy[j] : 0.0;
+                rsyq[q] = vj[q] ? p.rsy[j] : 0.0;
+                orow[q] = p.out + (int64_t)(xa + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
+                if (vj[q] && (p.push_mask & 4u) && j == 0) {
+                    yq = q;
+                    yptr = p.dst[2] + xa * p.sa[2] + kk;
+                    ystep = p.sa[2];
                 }
-                orow[q] += ps;
+                if (vj[q] && (p.push_mask & 8u) && j == p.Y - 1) {
+                    yq = q;
+                    yptr = p.dst[3] + xa * p.sa[3] + kk;
+                    ystep = p.sa[3];
+                }
             }
+            const bool zany = zpa != nullptr || zpb != nullptr;
+            const double szk0 = vk0 ? p.sz[kk] : 0.0, szk1 = vk1 ? p.sz[kk + 1] : 0.0;
+            const double rsz0 = vk0 ? p.rsz[kk] : 0.0, rsz1 = vk1 ? p.rsz[kk + 1] : 0.0;
 
-            // this warp is done with plane i-1 (source ring) and in-place plane i
+            // first two source planes of the segment
+            mbar_wait(full1 + 8u * fi, fph);
+            uint32_t am = ring1 + (uint32_t)fi * slot1_bytes;
+            if (++fi == p.s1) { fi = 0; fph ^= 1; }
+            mbar_wait(full1 + 8u * fi, fph);
+            uint32_t ac = ring1 + (uint32_t)fi * slot1_bytes;
+            if (++fi == p.s1) { fi = 0; fph ^= 1; }
+
+            for (int t = 0; t < nplanes; t++) {
+                const int i = xa + t;  // owned x index of the centre plane
+                mbar_wait(full1 + 8u * fi, fph);
+                const uint32_t ap = ring1 + (uint32_t)fi * slot1_bytes;
+                if (++fi == p.s1) { fi = 0; fph ^= 1; }
+                uint32_t a0 = 0;
+                if (!FIRST) {
+                    mbar_wait(full0 + 8u * f0i, f0ph);
+                    a0 = ring0 + (uint32_t)f0i * slot0_bytes;
+                }
+
+                const bool ei = i >= p.elo0 && i <= p.ehi0;
+                const double cs = __dmul_rn(cosn, __ldg(p.sx + i));
+                const double rcs = __dmul_rn(rcos, __ldg(p.rsx + i));
+                const bool pslow = xpush && (i == p.send_x0 || i == p.send_x1);
+
+                double2 rowc[RJ + 2];
+#pragma unroll
+                for (int q = 0; q < RJ + 2; q++) rowc[q] = lds2(ac + toff1 + (uint32_t)(q * kW1 * 8));
+
+#pragma unroll
+                for (int q = 0; q < RJ; q++) {
+                    const uint32_t rc = toff1 + (uint32_t)((q + 1) * kW1 * 8);
+                    const double2 c = rowc[q + 1], ym = rowc[q], yp = rowc[q + 2];
+                    const double zl = lds1(ac + rc - 8u);
+                    const double zr = lds1(ac + rc + 16u);
+                    const double2 xm = lds2(am + rc);
+                    const double2 xp = lds2(ap + rc);
+                    double2 g0 = c;
+                    if (!FIRST) g0 = lds2(a0 + toff0 + (uint32_t)(q * kTZ * 8));
+
+                    // exact expression order of the reference build
+                    const double c2a = __dadd_rn(c.x, c.x), c2b = __dadd_rn(c.y, c.y);
+                    const double sa_ = FIRST ? c.x : __dsub_rn(c2a, g0.x);
+                    const double sb_ = FIRST ? c.y : __dsub_rn(c2b, g0.y);
+                    const double lxa = div_const<DIV>(__dsub_rn(__dadd_rn(xp.x, xm.x), c2a), hx2, rx);
+                    const double lxb = div_const<DIV>(__dsub_rn(__dadd_rn(xp.y, xm.y), c2b), hx2, rx);
+                    const double lya = div_const<DIV>(__dsub_rn(__dadd_rn(yp.x, ym.x), c2a), hy2, ry);
+                    const double lyb = div_const<DIV>(__dsub_rn(__dadd_rn(yp.y, ym.y), c2b), hy2, ry);
+                    const double lza = div_const<DIV>(__dsub_rn(__dadd_rn(c.y, zl), c2a), hz2, rz);
+                    const double lzb = div_const<DIV>(__dsub_rn(__dadd_rn(zr, c.x), c2b), hz2, rz);
+                    const double ua = __fma_rn(coef, __dadd_rn(__dadd_rn(lxa, lya), lza), sa_);
+                    const double ub = __fma_rn(coef, __dadd_rn(__dadd_rn(lxb, lyb), lzb), sb_);
+
+                    if (vj[q]) {
+                        if (vk1) *reinterpret_cast<double2*>(orow[q]) = make_double2(ua, ub);
+                        else *orow[q] = ua;
+                        if (pslow) push_row_x(p, i, jr + q, kk, ua, ub, vk1);
+                        if (q == yq) store_pair(yptr, ua, ub, vk1);
+                        if (zany) {
+                            if (zpa) zpa[q * zsb] = ua;
+                            if (zpb && vk1) zpb[q * zsb] = ub;
+                        }
+                        if (ei) {
+                            const double fxy = __dmul_rn(cs, syq[q]);
+                            const double rxy = __dmul_rn(rcs, rsyq[q]);
+                            if (vk1) err_row<true>(ea, ua, ub, fxy, rxy, szk0, szk1, rsz0, rsz1);
+                            else err_row<false>(ea, ua, ub, fxy, rxy, szk0, szk1, rsz0, rsz1);
+                        }
+                    }
+                    orow[q] += ps;
+                }
+                if (yq >= 0) yptr += ystep;
+                if (zany) {
+                    if (zpa) zpa += zstep;
+                    if (zpb) zpb += zstep;
+                }
+
+                // this warp is done with source plane i-1 and in-place plane i
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(empty1 + 8u * bi);
+                    if (!FIRST) mbar_arrive(empty0 + 8u * f0i);
+                }
+                if (++bi == p.s1) bi = 0;
+                if (!FIRST) {
+                    if (++f0i == p.s0) { f0i = 0; f0ph ^= 1; }
+                }
+                am = ac;
+                ac = ap;
+            }
+            // the last two source planes of the segment are no longer needed either
             __syncwarp();
             if (lane == 0) {
-                mbar_arrive(bem);
-                if (!FIRST) mbar_arrive(be0);
+                mbar_arrive(empty1 + 8u * bi);
+                mbar_arrive(empty1 + 8u * (bi + 1 == p.s1 ? 0 : bi + 1));
             }
-            // rotate: (i-1, i, i+1) <- (i, i+1, i+2)
-            am = ac;
-            ac = ap;
-            ap += slot1_bytes;
-            bfp += 8u;
-            if (ap == ring1_end) { ap = ring1; bfp = full1; php ^= 1; }
-            bem += 8u;
-            if (bem == empty1_end) bem = empty1;
-            if (!FIRST) {
-                a0 += slot0_bytes;
-                bf0 += 8u;
-                be0 += 8u;
-                if (a0 == ring0_end) { a0 = ring0; bf0 = full0; be0 = empty0; ph0 ^= 1; }
-            }
+            bi += 2;
+            if (bi >= p.s1) bi -= p.s1;
         }
 
         // ---- error maxima: warp -> CTA
@@ -752,7 +810,7 @@ int launch_step(const StepLaunch& a) {
         return -1;
     }
     if (pl->warps < 1 || pl->warps > kMaxWarps || pl->ty != pl->rj * pl->warps || pl->tz != 64 || pl->s1 < 3 ||
-        pl->s0 < 1) {
+        pl->s0 < 1 || pl->ctas < 1) {
         set_last_error("invalid tile plan");
         return -1;
     }
@@ -796,7 +854,7 @@ int launch_step(const StepLaunch& a) {
     StepKernel k = pick_kernel(pl->rj, a.first != 0, div);
     const int smem = plan_smem_bytes(pl->ty, pl->tz, pl->s1, a.first ? 0 : pl->s0);
     if (ensure_smem_attr((const void*)k, smem)) return -1;
-    const int grid = pl->nty * pl->ntz * pl->nchunks;
+    const int grid = pl->ctas;  // persistent CTAs, each takes an equal share of the (tile, plane) units
     k<<<grid, (pl->warps + 1) * 32, smem, a.stream>>>(p);  // + the TMA producer warp
     W3D_TRY(cudaGetLastError());
     return 0;

@@ -288,13 +288,13 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
     int nov = 0;
     if (const char* e = getenv("WAVE3D_TILE")) nov = sscanf(e, "%d,%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3], &ov[4]);
     for (int rj = 1; rj <= 4; rj *= 2) {
-        for (int warps = 2; warps <= 11; warps++) {
+        for (int warps = 2; warps <= 7; warps++) {
             const int ty = rj * warps;
-            if (ty > 64) continue;
             if (nov >= 2 && (ty != ov[0] || rj != ov[1])) continue;
             int s1 = nov >= 4 ? ov[3] : 6, s0 = nov >= 5 ? ov[4] : 4;
             int smem = plan_smem_bytes(ty, tz, s1, s0);
-            while (smem > 220 * 1024 && s1 > 4) {
+            // keep two CTAs per SM when a shallower ring makes that possible
+            while (smem > 112 * 1024 && s1 > 4) {
                 s1--;
                 if (s0 > 2) s0--;
                 smem = plan_smem_bytes(ty, tz, s1, s0);
@@ -303,31 +303,36 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
             int occ = 0;
             if (have_gpu) occ = step_occupancy(rj, warps, smem);
             if (occ <= 0) {
-                occ = std::min(232448 / (smem + 1024), std::min(64 / (warps + 1), 18 / (warps + 1)));
+                occ = std::min(232448 / (smem + 1024), std::min(64 / (warps + 1), 16 / (warps + 1)));
                 if (occ < 1) occ = 1;
             }
             const int nty = (ny + ty - 1) / ty;
-            const int maxc = std::max(1, std::min(64, X / 8));
-            for (int nc = 1; nc <= maxc; nc++) {
-                if (nov >= 3 && nc != ov[2]) continue;
-                const int64_t items = (int64_t)nty * ntz * nc;
-                const double planes = std::ceil((double)X / nc);
-                // Bandwidth-bound model: an SM drains its CTAs at a fixed rate, so the
-                // kernel time follows the most loaded SM; chunk starts re-read 2 source
-                // planes (1/3 of the traffic); halo rings mostly hit L2.
-                const double halo = (double)(ty + 2) * (tz + 4) / ((double)ty * tz) - 1.0;
-                const double cta_cost = (planes + 2.0 / 3.0) * ty * tz * (1.0 + 0.2 * halo);
-                const double per_sm = std::ceil((double)items / sms);
-                double eff = (double)X * ny * nz / (per_sm * cta_cost * sms);
-                if (occ == 1 && items > sms) eff *= 0.9;          // nothing to overlap a CTA's barriers with
-                if (items < (int64_t)sms * occ && occ > 1) eff *= 0.97;  // fewer resident warps to hide latency
-                if (eff > best + 1e-9) {
-                    best = eff;
-                    plan->tz = tz; plan->ty = ty; plan->rj = rj; plan->warps = warps;
-                    plan->nty = nty; plan->ntz = ntz; plan->nchunks = nc;
-                    plan->s1 = s1; plan->s0 = s0; plan->smem_bytes = smem;
-                    plan->ctas = (int)items; plan->slots = sms * occ; plan->efficiency = eff;
-                }
+            const int64_t units = (int64_t)nty * ntz * X;  // (tile, x-plane) work units, dealt out evenly
+            int64_t ctas = (int64_t)sms * occ;
+            if (ctas > units / 4) ctas = std::max<int64_t>(1, units / 4);
+            if (nov >= 3 && ov[2] > 0) ctas = ov[2];
+            // Bandwidth-bound model of the persistent kernel: every CTA gets units/ctas planes of a
+            // ty x 64 tile. Losses: masked cells of ragged tiles, halo ring of the source boxes
+            // (mostly L2 hits), ring restarts when a CTA crosses into the next tile column,
+            // RJ=1 spends more shared-memory traffic and instructions per cell, one CTA per SM
+            // has nothing to overlap its own stalls with.
+            const double waste = (double)nty * ty * ntz * tz / ((double)ny * nz);
+            const double halo = (double)(ty + 2) * (tz + 4) / ((double)ty * tz) - 1.0;
+            const double per_cta = (double)units / (double)ctas;
+            const double restart = 1.0 + 4.5 / per_cta;
+            const double rjf = rj == 1 ? 1.12 : (rj == 2 ? 1.0 : 1.02);
+            const double occf = occ >= 2 ? 1.0 : 1.25;
+            const int tlp = occ * warps;  // compute warps per SM; ~14 are needed to cover the LDS/FP64 latencies
+            const double tlpf = tlp >= 14 ? 1.0 : 1.0 + 0.04 * (14 - tlp);
+            const double fill = (double)(sms * occ) / (double)ctas;  // > 1 when the box is too small to fill the GPU
+            const double eff = 1.0 / (waste * (1.0 + 0.3 * halo) * restart * rjf * occf * tlpf * std::max(1.0, fill));
+            if (eff > best + 1e-9) {
+                best = eff;
+                plan->tz = tz; plan->ty = ty; plan->rj = rj; plan->warps = warps;
+                plan->nty = nty; plan->ntz = ntz;
+                plan->nchunks = (int)((ctas + (int64_t)nty * ntz - 1) / ((int64_t)nty * ntz));
+                plan->s1 = s1; plan->s0 = s0; plan->smem_bytes = smem;
+                plan->ctas = (int)ctas; plan->slots = sms * occ; plan->efficiency = eff;
             }
         }
     }

@@ -182,15 +182,16 @@ typedef struct wave3d_plan {
     int32_t ty;      /* tile height in y = rj * warps */
     int32_t rj;      /* rows per warp */
     int32_t warps;   /* warps per CTA */
-    int32_t nty, ntz, nchunks;
+    int32_t nty, ntz; /* tiles in y and z */
+    int32_t nchunks;  /* informational: CTAs per tile column (rounded up) */
     int32_t s1, s0;  /* ring depth: stencil-source planes / in-place planes */
     int32_t smem_bytes;
-    int32_t ctas;    /* nty*ntz*nchunks */
+    int32_t ctas;    /* persistent CTAs; each marches an equal share of the nty*ntz*X (tile, plane) units */
     int32_t slots;   /* resident CTAs on the device */
     double efficiency; /* modelled useful fraction */
 } wave3d_plan;
 
-/* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,nchunks[,s1,s0]" overrides. */
+/* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,ctas[,s1,s0]" overrides (ctas 0 = auto). */
 void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan);
 
 /* --- kernel-level entry points (device pointers; stream = cudaStream_t or 0) --- */

@@ -16,12 +16,12 @@ nvidia-smi topo -m > $OUT/topo.txt 2>&1
 for n in 1 2 4 8; do [ $n -le $G ] && tr $n ours_N512_$n --steps 20 --warmup 3; done
 for n in 1 2 4 8; do [ $n -le $G ] && tr $n ref_N512_$n --impl reference --steps 20 --warmup 3; done
 if [ $G -ge 8 ]; then
-  tr 8 ours_N1024_8_3d --n 1024 --steps 20 --warmup 3
-  tr 8 ours_N1024_8_1d --n 1024 --steps 20 --warmup 3 --dims 8x1x1
+  tr 8 ours_N1024_8_3d --grid 1024 --steps 20 --warmup 3
+  tr 8 ours_N1024_8_1d --grid 1024 --steps 20 --warmup 3 --dims 8x1x1
   tr 8 ours_N512_8_staged --steps 20 --warmup 3 --transport staged
-  tr 8 ours_N2048_8 --n 2048 --steps 10 --warmup 3 --repeats 3
-  tr 8 ref_N1024_8 --impl reference --n 1024 --steps 20 --warmup 3
+  tr 8 ours_N2048_8 --grid 2048 --steps 10 --warmup 3 --repeats 3
+  tr 8 ref_N1024_8 --impl reference --grid 1024 --steps 20 --warmup 3
 fi
-tr 1 ours_N1024_1 --n 1024 --steps 20 --warmup 3 --repeats 3
-tr 1 ours_N256pi_1 --n 256 --length pi --steps 20 --warmup 3
-tr 1 ref_N256pi_1 --impl reference --n 256 --length pi --steps 20 --warmup 3
+tr 1 ours_N1024_1 --grid 1024 --steps 20 --warmup 3 --repeats 3
+tr 1 ours_N256pi_1 --grid 256 --length pi --steps 20 --warmup 3
+tr 1 ref_N256pi_1 --impl reference --grid 256 --length pi --steps 20 --warmup 3
