@@ -307,32 +307,60 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
                 if (occ < 1) occ = 1;
             }
             const int nty = (ny + ty - 1) / ty;
-            const int64_t units = (int64_t)nty * ntz * X;  // (tile, x-plane) work units, dealt out evenly
-            int64_t ctas = (int64_t)sms * occ;
-            if (ctas > units / 4) ctas = std::max<int64_t>(1, units / 4);
-            if (nov >= 3 && ov[2] > 0) ctas = ov[2];
-            // Bandwidth-bound model of the persistent kernel: every CTA gets units/ctas planes of a
-            // ty x 64 tile. Losses: masked cells of ragged tiles, halo ring of the source boxes
-            // (mostly L2 hits), ring restarts when a CTA crosses into the next tile column,
-            // RJ=1 spends more shared-memory traffic and instructions per cell, one CTA per SM
-            // has nothing to overlap its own stalls with.
+            const int ntiles = nty * ntz;
+            const int slots = sms * occ;
+            // Model (bandwidth bound, calibrated on B200): a CTA spends (planes + r0) plane-times per
+            // item, r0 = extra x-halo planes + segment set-up; CTAs work in rounds of `ctas` items, all
+            // CTAs of a round in the same x range. Losses: masked cells of ragged tiles, halo ring of the
+            // source boxes (L2 hits), RJ=1 spends more shared-memory traffic and instructions per cell,
+            // few warps per SM cannot cover the LDS/FP64 latencies, unfilled last round.
             const double waste = (double)nty * ty * ntz * tz / ((double)ny * nz);
             const double halo = (double)(ty + 2) * (tz + 4) / ((double)ty * tz) - 1.0;
-            const double per_cta = (double)units / (double)ctas;
-            const double restart = 1.0 + 4.5 / per_cta;
-            const double rjf = rj == 1 ? 1.12 : (rj == 2 ? 1.0 : 1.02);
+            const double rjf = rj == 1 ? 1.12 : (rj == 2 ? 1.0 : 1.08);
             const double occf = occ >= 2 ? 1.0 : 1.25;
-            const int tlp = occ * warps;  // compute warps per SM; ~14 are needed to cover the LDS/FP64 latencies
+            const int tlp = occ * warps;
             const double tlpf = tlp >= 14 ? 1.0 : 1.0 + 0.04 * (14 - tlp);
-            const double fill = (double)(sms * occ) / (double)ctas;  // > 1 when the box is too small to fill the GPU
-            const double eff = 1.0 / (waste * (1.0 + 0.3 * halo) * restart * rjf * occf * tlpf * std::max(1.0, fill));
+            const double r0 = 1.5;  // plane-times lost per item: two extra x-halo planes + segment set-up
+            const int ctas = (int)std::min<int64_t>(slots, (int64_t)ntiles * std::max(1, X / 6));
+            // guided chunk lengths: start near 60 % of a CTA's share (never more than half a column),
+            // halve down to a floor that bounds the end-of-kernel imbalance
+            const double share = (double)ntiles * X / ctas;
+            const int minlen = std::max(4, std::min(X, std::max(8, X / 32)));
+            int cuts[18];
+            int m = 0;
+            cuts[0] = 0;
+            if (nov >= 3 && ov[2] > 0) {
+                m = std::min(16, std::min(ov[2], X));
+                for (int c = 1; c <= m; c++) cuts[c] = (int)((int64_t)X * c / m);
+            } else {
+                // built from the end of the column: two floor-sized chunks, then doubling up to the cap;
+                // what is left over goes to the front, where imbalance can still be repaired
+                const int cap = std::max(minlen, (int)std::min(X / 2.0, share * 0.6));
+                int len[16];
+                int left = X, l = minlen, k = 0;
+                while (left > 0 && k < 16) {
+                    int take = std::min(l, left);
+                    if (k == 15 || left - take < minlen) take = left;
+                    len[k++] = take;
+                    left -= take;
+                    if (k >= 2) l = std::min(cap, l * 2);
+                }
+                m = k;  // len[] is in back-to-front order
+                std::sort(len, len + m);
+                for (int c = 0; c < m; c++) cuts[c + 1] = cuts[c] + len[m - 1 - c];
+            }
+            const double tail = 0.5 * (cuts[m] - cuts[m - 1]) / std::max(1.0, share);
+            const double fill = std::max(1.0, (double)slots / ((double)ntiles * m));
+            const double eff = (double)X / (X + m * r0) / (1.0 + tail) / fill /
+                               (waste * (1.0 + 0.3 * halo) * rjf * occf * tlpf);
             if (eff > best + 1e-9) {
                 best = eff;
                 plan->tz = tz; plan->ty = ty; plan->rj = rj; plan->warps = warps;
-                plan->nty = nty; plan->ntz = ntz;
-                plan->nchunks = (int)((ctas + (int64_t)nty * ntz - 1) / ((int64_t)nty * ntz));
+                plan->nty = nty; plan->ntz = ntz; plan->nchunks = m;
                 plan->s1 = s1; plan->s0 = s0; plan->smem_bytes = smem;
-                plan->ctas = (int)ctas; plan->slots = sms * occ; plan->efficiency = eff;
+                plan->ctas = (int)std::min<int64_t>(ctas, (int64_t)ntiles * m);
+                plan->slots = slots; plan->efficiency = eff;
+                for (int c = 0; c <= m; c++) plan->xcut[c] = cuts[c];
             }
         }
     }

@@ -245,6 +245,7 @@ void wave3d_layout_init(const wave3d_box* b, wave3d_layout* l) {
     l->oz = 16 - b->lo[2];
     int64_t need = (int64_t)l->oz + b->n[2] + 1;  // up to and including the z+ ghost column
     l->pitch = (need + 15) / 16 * 16;
+    if (const char* e = getenv("WAVE3D_PITCH_PAD")) l->pitch += 16 * (int64_t)atoi(e);  // tuning: extra 128-byte lines per row
     l->rows = (int64_t)b->n[1] + 2;
     l->planes = (int64_t)b->n[0] + 2;
     l->plane_stride = l->rows * l->pitch;

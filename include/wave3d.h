@@ -183,15 +183,16 @@ typedef struct wave3d_plan {
     int32_t rj;      /* rows per warp */
     int32_t warps;   /* warps per CTA */
     int32_t nty, ntz; /* tiles in y and z */
-    int32_t nchunks;  /* informational: CTAs per tile column (rounded up) */
+    int32_t nchunks;  /* x-chunks per tile column (<= 16); items = nty*ntz*nchunks, handed out dynamically */
     int32_t s1, s0;  /* ring depth: stencil-source planes / in-place planes */
     int32_t smem_bytes;
-    int32_t ctas;    /* persistent CTAs; each marches an equal share of the nty*ntz*X (tile, plane) units */
+    int32_t ctas;    /* persistent CTAs pulling (tile, x-chunk) items from a device-side queue, chunk-major */
     int32_t slots;   /* resident CTAs on the device */
     double efficiency; /* modelled useful fraction */
+    int32_t xcut[18];  /* chunk c covers owned planes [xcut[c], xcut[c+1]); sizes shrink towards the end */
 } wave3d_plan;
 
-/* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,ctas[,s1,s0]" overrides (ctas 0 = auto). */
+/* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,nchunks[,s1,s0]" overrides (nchunks 0 = auto). */
 void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan);
 
 /* --- kernel-level entry points (device pointers; stream = cudaStream_t or 0) --- */
@@ -219,7 +220,7 @@ typedef struct wave3d_peers {
     uint64_t* root_err;    /* rank 0's error table (2*(timesteps+1) u64) or NULL */
 } wave3d_peers;
 
-/* Scratch words of one rank: [0] CTA ticket, [1] status (0 ok, 1 spin timeout), rest reserved. */
+/* Scratch words of one rank: [0] CTA ticket, [1] status (0 ok, 1 spin timeout), [2] work queue, rest reserved. */
 #define WAVE3D_SCRATCH_WORDS 16
 
 /* The fused step (ref K2/K3 + K4 + K5 + K6 + K7 + memsets + MPI p2p):

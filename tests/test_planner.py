@@ -20,12 +20,14 @@ def test_plan_is_feasible(N, nranks, dims):
         assert pl.nty * pl.ty >= box.hi[1] - box.lo[1] + 1
         assert pl.ntz * pl.tz >= box.hi[2] - box.lo[2] + 1
         assert pl.smem_bytes <= 227 * 1024 and pl.s1 >= 3 and pl.s0 >= 1
-        assert 1 <= pl.ctas <= pl.slots
+        assert 1 <= pl.ctas <= pl.slots and pl.ctas <= pl.nty * pl.ntz * pl.nchunks
+        assert 1 <= pl.nchunks <= 16 and pl.xcut[0] == 0 and pl.xcut[pl.nchunks] == box.n[0]
+        assert all(pl.xcut[c] < pl.xcut[c + 1] for c in range(pl.nchunks))
         assert (0.3 if N >= 256 else 0.0) < pl.efficiency <= 1.0
 
 
 def test_plan_override(monkeypatch):
-    monkeypatch.setenv("WAVE3D_TILE", "12,2,100")
+    monkeypatch.setenv("WAVE3D_TILE", "12,2,3")
     box = Decomposition.create(256, 1).box(0)
     pl = K.plan_for(box, 148)
-    assert (pl.ty, pl.rj, pl.warps, pl.ctas) == (12, 2, 6, 100)
+    assert (pl.ty, pl.rj, pl.warps, pl.nchunks) == (12, 2, 6, 3)
