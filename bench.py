@@ -141,6 +141,16 @@ def run_ours(a):
                "d2h_bytes_per_step": 16, "ms_per_step": t_e2e / K,
                "note": "per step: pinned->device copy of the step descriptor, fused kernel, device->host read of "
                        "the step's max abs/rel error, stream sync; wall clock, max over ranks"}
+    # roofline: 24 B of HBM traffic per cell per step (read u^{n-1}, read u^{n-2}, write u^n) against the
+    # MEASURED copy bandwidth of this pool (MEASURED_PEAKS.json; fallback 6650 GB/s, B200_PROFILING.md)
+    hbm, src = 6650.0, "fallback"
+    try:
+        hbm, src = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:  # noqa: BLE001
+        pass
+    roof = a.gpus * hbm / 24.0
+    roofline = {"bytes_per_cell_step": 24, "hbm_gbs_per_gpu": hbm, "basis": f"of {src}", "roofline_gcells": roof,
+                "fraction": value / roof}
     out = {
         "metric": "Gcell-updates/s (device-timed, max over ranks)", "value": value, "unit": "Gcell-updates/s",
         "n_gpus": a.gpus, "steps": K, "warmup": a.warmup, "ms_per_step": t_ms / K, "higher_is_better": True,
@@ -157,6 +167,7 @@ def run_ours(a):
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
                    "reasons": clocks.get("reasons", []), "samples": clocks.get("samples")},
         "gpu_launches": int(launches),
+        "roofline": roofline,
     }
     if e2e:
         out["e2e"] = e2e

@@ -963,7 +963,29 @@ int wave3d_main(int argc, const char* const* argv) {
     }
     auto t1 = std::chrono::steady_clock::now();
     wave3d_timings tm;
-    int rc = wave3d_solver_run(s, &tm);
+    int rc = 0;
+    const char* prog = getenv("WAVE3D_PROGRESS");
+    if (prog && atoi(prog)) {
+        // reference-style driver: one line per layer on stdout and the layer's maxima read back
+        // before the next layer starts (ref: cuda_sol.cpp:338,385 "calculating layer n")
+        memset(&tm, 0, sizeof tm);
+        const bool staged = o.backend == WAVE3D_BACKEND_CPU || o.transport == WAVE3D_TRANSPORT_STAGED;
+        auto w0 = std::chrono::steady_clock::now();
+        rc = wave3d_solver_reset(s) || wave3d_solver_enqueue_layer0(s);
+        if (!rc && staged) rc = wave3d_solver_exchange_local(s, 0);
+        double e2[2];
+        for (int n = 1; !rc && n <= p.timesteps; n++) {
+            printf("calculating layer %d\n", n);
+            fflush(stdout);
+            rc = wave3d_solver_enqueue_step(s, n);
+            if (!rc && staged && n < p.timesteps) rc = wave3d_solver_exchange_local(s, n);
+            if (!rc) rc = wave3d_solver_layer_error(s, n, e2);
+        }
+        if (!rc) rc = wave3d_solver_sync(s);
+        tm.solve_ms = tm.loop_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+    } else {
+        rc = wave3d_solver_run(s, &tm);
+    }
     if (rc) {
         fprintf(stderr, "wave3d: solve failed: %s\n", wave3d_cuda_last_error());
         wave3d_solver_destroy(s);

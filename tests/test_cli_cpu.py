@@ -37,3 +37,13 @@ def test_cli_cpu_decomposed_full_precision(tmp_path):
 def test_cli_usage_error(tmp_path):
     r = _run([32, 1], tmp_path)
     assert r.returncode == 2 and "usage" in r.stderr
+
+
+def test_cli_progress_mode_matches_batch_mode(tmp_path):
+    a = _run([20, 1, 1, 1, 1, 0.025, 4], tmp_path, WAVE3D_FULL_PRECISION="1", WAVE3D_OUTPUT="a.txt", WAVE3D_RANKS="4")
+    b = _run([20, 1, 1, 1, 1, 0.025, 4], tmp_path, WAVE3D_FULL_PRECISION="1", WAVE3D_OUTPUT="b.txt", WAVE3D_RANKS="4",
+             WAVE3D_PROGRESS="1")
+    assert a.returncode == 0 and b.returncode == 0
+    assert [l for l in b.stdout.splitlines() if l.startswith("calculating layer")] == \
+        [f"calculating layer {n}" for n in range(1, 5)]  # ref: cuda_sol.cpp:338,385
+    assert (tmp_path / "a.txt.full").read_text().splitlines()[1:] == (tmp_path / "b.txt.full").read_text().splitlines()[1:]
