@@ -67,7 +67,8 @@ class SolverOpts(C.Structure):
     _fields_ = [("backend", C.c_int32), ("transport", C.c_int32), ("dims", C.c_int32 * 3), ("nranks", C.c_int32),
                 ("first_rank", C.c_int32), ("nlocal", C.c_int32), ("devices", C.c_int32 * 8),
                 ("use_graph", C.c_int32), ("threads", C.c_int32), ("per_step_sync", C.c_int32),
-                ("verbose", C.c_int32), ("spin_timeout_s", C.c_double)]
+                ("verbose", C.c_int32), ("multistep", C.c_int32), ("reserved", C.c_int32),
+                ("spin_timeout_s", C.c_double)]
 
 
 class Export(C.Structure):

@@ -27,7 +27,8 @@ from .wave import SolveResult, WaveSolver
 
 class DistributedWaveSolver:
     def __init__(self, problem: Problem, dims: Optional[Sequence[int]] = None, backend: Optional[str] = None,
-                 transport: str = "auto", use_graph: bool = True, threads: int = 0, spin_timeout_s: float = 10.0):
+                 transport: str = "auto", use_graph: bool = True, threads: int = 0, spin_timeout_s: float = 10.0,
+                 multistep: bool = True):
         if not dist.is_initialized():
             pdist.init_process_group_from_env()
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
@@ -45,7 +46,8 @@ class DistributedWaveSolver:
         self.transport = "peer" if want_peer else "staged"
         mk = lambda tr: WaveSolver(problem, nranks=self.world, dims=dims, backend=backend, transport=tr,
                                    devices=[self.dev_index] if backend == "cuda" else None, use_graph=use_graph,
-                                   threads=threads, first_rank=self.rank, nlocal=1, spin_timeout_s=spin_timeout_s)
+                                   threads=threads, first_rank=self.rank, nlocal=1, spin_timeout_s=spin_timeout_s,
+                                   multistep=multistep)
         self.inner = mk(self.transport)
         if want_peer:
             ok, why = True, ""

@@ -47,7 +47,7 @@ class WaveSolver:
     def __init__(self, problem: Problem, nranks: int = 1, dims: Optional[Sequence[int]] = None, backend: str = "cuda",
                  transport: str = "peer", devices: Optional[Sequence[int]] = None, use_graph: bool = True,
                  threads: int = 0, per_step_sync: bool = False, first_rank: int = 0, nlocal: Optional[int] = None,
-                 spin_timeout_s: float = 10.0):
+                 spin_timeout_s: float = 10.0, multistep: bool = True):
         self.problem = problem
         self._p = problem.native()
         o = _lib.SolverOpts()
@@ -68,6 +68,7 @@ class WaveSolver:
         o.threads = threads
         o.per_step_sync = int(per_step_sync)
         o.spin_timeout_s = spin_timeout_s
+        o.multistep = int(multistep)
         self.opts = o
         self.backend = backend
         self.transport = transport

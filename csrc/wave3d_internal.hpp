@@ -28,19 +28,22 @@ int choose_div_mode(const wave3d_problem* p);
 // Pre-encoded arguments of one fused-step launch (maps are encoded once per field
 // by the runtime and reused for every step).
 struct StepLaunch {
-    CUtensorMap map_src;  // halo box (tz+4, ty+2, 1) over the stencil source layer
-    CUtensorMap map_io;   // core box (tz, ty, 1) over the in-place layer
+    CUtensorMap map_halo[2];  // per field: halo box (tz+4, ty+2, 1), used when the field is the stencil source
+    CUtensorMap map_core[2];  // per field: core box (tz, ty, 1), used when the field is updated in place
     const wave3d_problem* prob;
     const wave3d_box* box;
     const wave3d_layout* lay;
     const wave3d_plan* plan;
     const double* tabs[6];
-    double* u_io;
-    int n;
+    double* field[2];   // layer n lives in field n & 1
+    int n;              // (first) layer computed by the launch
+    int nsteps;         // 1: one layer per launch; > 1: layers n .. n+nsteps-1 in one persistent cooperative launch
     int first;
-    wave3d_peers peers;  // zero-initialised when absent
+    wave3d_peers peers[2];  // per written field; zero-initialised when absent
     uint64_t* err;       // table base (2 words per layer)
     uint32_t* scratch;
+    uint32_t* epoch;     // multi-layer launches: one word per (tile, chunk) item, zeroed before the solve
+    uint32_t* stepdone;  // multi-layer launches: one word per layer, zeroed before the solve
     const double* desc;  // device pointer to {arg_t, coef} or nullptr
     double spin_timeout_s;
     int div_mode;        // -1: choose

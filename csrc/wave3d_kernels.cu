@@ -65,6 +65,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             : "memory");
     } while (!done);
 }
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return done != 0;
+}
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
@@ -88,28 +99,32 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // ------------------------------------------------------------- step parameters
 
 struct alignas(64) StepParams {
-    CUtensorMap map_src;
-    CUtensorMap map_io;
-    double* out;
+    CUtensorMap map_halo[2];  // per field: halo box (tz+4, ty+2, 1) — used when the field is the stencil source
+    CUtensorMap map_core[2];  // per field: core box (tz, ty, 1)    — used when the field is updated in place
+    double* field[2];         // layer n lives in field n & 1
     const double* sx;
     const double* sy;
     const double* sz;
     const double* rsx;
     const double* rsy;
     const double* rsz;
-    double* dst[6];
+    double* dst[2][6];        // per written field: neighbour ghost cell that receives my face cell (0,0)
     int64_t sa[6];
     int64_t sb[6];
     uint32_t* flag_out[6];
     const uint32_t* flag_in[6];
-    uint64_t* err;       // &table[2n]
-    uint64_t* root_err;  // &root_table[2n] or nullptr
+    uint64_t* err;       // table base: layer n -> err[2n], err[2n+1]
+    uint64_t* root_err;  // rank 0's table base or nullptr
     uint32_t* scratch;
-    const double* desc;  // optional uploaded step descriptor {arg_t, coef}
+    uint32_t* epoch;     // multi-step mode: last completed layer per (tile, chunk) item
+    uint32_t* stepdone;  // multi-step mode: completed items per layer
+    const double* desc;  // optional uploaded step descriptor {arg_t, coef} (single-step mode)
     int64_t ps, pitch;
     double coef, arg_t;
+    double a_t, tau, twopi;  // multi-step mode: cos(fma(a_t*n, tau, twopi)) per layer
     double hx2, hy2, hz2, rx, ry, rz;
     unsigned long long timeout_ns;
+    int n0, nsteps;          // layers n0 .. n0+nsteps-1 are computed by this launch
     int oz, X, Y, Z;
     int lo1, hi1, lo2, hi2;
     int elo0, ehi0;
@@ -117,11 +132,19 @@ struct alignas(64) StepParams {
     int xcut[18];
     int s1, s0;
     int send_x0, send_x1;
-    uint32_t epoch_wait, epoch_pub;
-    uint32_t push_mask;  // bit f set: dst[f] != nullptr
+    uint32_t push_mask;  // bit f set: dst[.][f] != nullptr
     int dbg;             // write phase timestamps into g_dbg_ts
-    int fence_mode;      // 0: no peers, gpu-scope fences only; 1: gpu per CTA + one sys fence in the last CTA; 2: sys in every CTA
+    int fence_mode;      // 0: no peers, gpu-scope fences only; 1: gpu per CTA + one sys fence per layer; 2: sys in every CTA
 };
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 // Division of a stencil sum by the constant d = h^2 with r = rn(1/d).
 template <int DIV>
@@ -214,9 +237,10 @@ __device__ __forceinline__ void store_pair(double* p, double a, double b, bool t
 // Face cells are stored a second time, straight into the neighbour's ghost cells (peer memory).
 // x faces: whole planes, hit on at most two planes per rank -> out of line; y and z faces are
 // stored inline in the march through per-thread pointers.
-__device__ __noinline__ void push_row_x(const StepParams& p, int i, int j, int kk, double ua, double ub, bool two) {
-    if ((p.push_mask & 1u) && i == p.send_x0) store_pair(p.dst[0] + j * p.sa[0] + kk, ua, ub, two);
-    if ((p.push_mask & 2u) && i == p.send_x1) store_pair(p.dst[1] + j * p.sa[1] + kk, ua, ub, two);
+__device__ __noinline__ void push_row_x(const StepParams& p, int w, int i, int j, int kk, double ua, double ub,
+                                        bool two) {
+    if ((p.push_mask & 1u) && i == p.send_x0) store_pair(p.dst[w][0] + j * p.sa[0] + kk, ua, ub, two);
+    if ((p.push_mask & 2u) && i == p.send_x1) store_pair(p.dst[w][1] + j * p.sa[1] + kk, ua, ub, two);
 }
 
 // Optional per-CTA phase timestamps of the last k_step launch (WAVE3D_DBG_TS=1; scripts/cta_timeline.py)
@@ -226,12 +250,20 @@ constexpr int kMaxWarps = 7;    // compute warps per CTA (one more warp is the T
 constexpr int kTZ = 64;         // tile width in z: one warp row = 32 lanes x 2 cells
 constexpr int kW1 = kTZ + 4;    // halo slot row length in doubles (2 halo columns each side keep 16-byte alignment)
 
-template <int RJ, bool FIRST, int DIV>
+// MULTI = false: one layer per launch (layer p.n0); the last CTA publishes the layer.
+// MULTI = true : layers n0 .. n0+nsteps-1 in ONE persistent launch. Items of consecutive layers form one
+//   queue; an item of layer n starts as soon as its own and its six face-adjacent items of layer n-1 are
+//   complete (per-item epoch words, release/acquire at gpu scope) and — only if it touches a rank face —
+//   the neighbour rank has published layer n-1. No grid-wide barrier, no launch gap, no kernel tail
+//   between layers: SMs that finish a layer early run ahead into the next one, interior items overlap
+//   the neighbours' flag latency. Needs all CTAs co-resident (cooperative launch).
+template <int RJ, bool FIRST, int DIV, bool MULTI>
 __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_constant__ StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_bcast[3];
     __shared__ double s_red[kMaxWarps][2];
     __shared__ int s_item[8];                // item ids handed from the producer lane to the compute warps
+    __shared__ __align__(8) uint64_t s_pbar[8];  // multi-step mode: compute warps -> producer lane, item finished
     __shared__ __align__(8) uint64_t s_ibar[8];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -244,6 +276,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
     const uint32_t full1 = bars, empty1 = full1 + 8u * (uint32_t)p.s1;
     const uint32_t full0 = empty1 + 8u * (uint32_t)p.s1, empty0 = full0 + 8u * (uint32_t)p.s0;
     const uint32_t ibar = smem_u32(s_ibar);
+    const uint32_t pbar = smem_u32(s_pbar);
 
     // ---- persistent CTAs pulling work from a device-side queue. Every tile column is cut into
     // p.nchunks x-chunks whose lengths shrink towards the end of the column (guided self-scheduling);
@@ -252,11 +285,15 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
     // memory bandwidth simply take more of the small late items (measured spread between SMs: 20 %).
     const int ntiles = p.nty * p.ntz;
     const int nitems = ntiles * p.nchunks;
+    const int ntotal = nitems * p.nsteps;
     const bool dbg = p.dbg && blockIdx.x < 2048;
     if (dbg && tid == 0) g_dbg_ts[blockIdx.x * 8 + 0] = globaltimer_ns();
 
     if (tid == 0) {
-        for (int s = 0; s < 8; s++) mbar_init(ibar + 8u * s, 1);
+        for (int s = 0; s < 8; s++) {
+            mbar_init(ibar + 8u * s, 1);
+            mbar_init(pbar + 8u * s, (uint32_t)ncw);
+        }
         for (int s = 0; s < p.s1; s++) {
             mbar_init(full1 + 8u * s, 1);
             mbar_init(empty1 + 8u * s, (uint32_t)ncw);
@@ -286,48 +323,139 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             // and they no longer read the ghosts this layer overwrites (WAR). Nothing of this CTA
             // touches global memory before its first plane has arrived, i.e. after this wait.
             const unsigned long long t0 = globaltimer_ns();
-            for (int f = 0; f < 6; f++) {
-                const uint32_t* fl = p.flag_in[f];
-                if (!fl) continue;
-                while (ld_acquire_sys(fl) < p.epoch_wait) {
+            auto wait_flag = [&](const uint32_t* fl, uint32_t need, bool sys) {
+                while ((sys ? ld_acquire_sys(fl) : ld_acquire_gpu(fl)) < need) {
                     __nanosleep(32);
                     if (globaltimer_ns() - t0 > p.timeout_ns) {
                         atomicExch(&p.scratch[1], 1u);
                         break;
                     }
                 }
+            };
+            if (!MULTI) {
+                for (int f = 0; f < 6; f++)
+                    if (p.flag_in[f]) wait_flag(p.flag_in[f], (uint32_t)p.n0, true);
+                asm volatile("fence.proxy.async;" ::: "memory");
             }
-            asm volatile("fence.proxy.async;" ::: "memory");
             const uint32_t box1_bytes = (uint32_t)((p.ty + 2) * kW1 * 8);
             const uint32_t box0_bytes = (uint32_t)(p.ty * kTZ * 8);
             int s1i = 0, s0i = 0;
             uint32_t ph1 = 1, ph0 = 1;  // parity of the "previous" phase: passes immediately on first use
+            // multi-layer mode: this lane also publishes finished items. It is idle most of the time, so
+            // the gpu-scope fence (which has to wait for the SM's outstanding stores) never sits on a
+            // compute warp's critical path; it is cumulative over the warps' block-scope arrivals.
+            int pub_kq = 0, issued_kq = 0;
+            int pub_gid[8];
+            auto publish = [&](bool block) {
+                while (MULTI && pub_kq < issued_kq) {
+                    const uint32_t bar = pbar + 8u * (pub_kq & 7), par = (uint32_t)((pub_kq >> 3) & 1);
+                    if (block) mbar_wait(bar, par);
+                    else if (!mbar_test(bar, par)) break;
+                    const int gid = pub_gid[pub_kq & 7];
+                    const int n = p.n0 + gid / nitems, item = gid % nitems;
+                    __threadfence();
+                    st_release_gpu(p.epoch + item, (uint32_t)n);
+                    if (atomicAdd(p.stepdone + n, 1u) == (uint32_t)nitems - 1u) {
+                        // layer n is complete on this rank
+                        unsigned long long* e = reinterpret_cast<unsigned long long*>(p.err + 2 * (size_t)n);
+                        if (p.fence_mode != 0) __threadfence_system();
+                        if (p.root_err) {
+                            const unsigned long long va = atomicMax(e, 0ull), vr = atomicMax(e + 1, 0ull);
+                            unsigned long long* re = reinterpret_cast<unsigned long long*>(p.root_err + 2 * (size_t)n);
+                            atomicMax_system(re, va);
+                            atomicMax_system(re + 1, vr);
+                        }
+                        for (int f = 0; f < 6; f++)
+                            if (p.flag_out[f]) st_release_sys(p.flag_out[f], (uint32_t)n + 1u);
+                    }
+                    pub_kq++;
+                }
+            };
             for (int kq = 0;; kq++) {
                 // the first item is the CTA's own index (no atomic on the critical path), later ones
                 // come from the queue, which starts at gridDim.x
-                int item = kq == 0 ? (int)blockIdx.x : (int)(gridDim.x + atomicAdd(&p.scratch[2], 1u));
-                if (item >= nitems) item = -1;
-                s_item[kq & 7] = item;
+                int gid = kq == 0 ? (int)blockIdx.x : (int)(gridDim.x + atomicAdd(&p.scratch[2], 1u));
+                if (gid >= ntotal) gid = -1;
+                s_item[kq & 7] = gid;
                 mbar_arrive(ibar + 8u * (kq & 7));  // release: the compute warps read s_item after this phase
-                if (item < 0) break;
+                if (gid < 0) {
+                    publish(true);
+                    break;
+                }
+                pub_gid[kq & 7] = gid;
+                issued_kq = kq + 1;
+                const int n = p.n0 + (MULTI ? gid / nitems : 0);
+                const int item = MULTI ? gid % nitems : gid;
+                const int w = n & 1;  // layer n is written into field w, the stencil source is field w^1
                 const int chunk = item / ntiles, tile = item - chunk * ntiles;
                 const int xa = p.xcut[chunk];
                 const int nplanes = p.xcut[chunk + 1] - xa;
-                const int j0 = p.lo1 + (tile / p.ntz) * p.ty;
-                const int k0 = p.lo2 + (tile % p.ntz) * kTZ;
+                const int tyi = tile / p.ntz, tzi = tile - tyi * p.ntz;
+                const int j0 = p.lo1 + tyi * p.ty;
+                const int k0 = p.lo2 + tzi * kTZ;
+                if (MULTI) {
+                    // RAW on the source layer and WAR on the in-place layer are both covered by "this item
+                    // and its face neighbours finished layer n-1"; items on a rank face also need the
+                    // neighbour rank's layer n-1 (published as epoch n). All words are polled together
+                    // (independent loads, one L2 round trip per poll), then one fence makes it an acquire.
+                    const uint32_t* wp[13];
+                    uint32_t wn[13];
+                    int nw = 0;
+                    if (n > p.n0) {
+                        const uint32_t need = (uint32_t)(n - 1);
+                        wp[nw] = p.epoch + item; wn[nw++] = need;
+                        if (chunk > 0) { wp[nw] = p.epoch + item - ntiles; wn[nw++] = need; }
+                        if (chunk + 1 < p.nchunks) { wp[nw] = p.epoch + item + ntiles; wn[nw++] = need; }
+                        if (tyi > 0) { wp[nw] = p.epoch + item - p.ntz; wn[nw++] = need; }
+                        if (tyi + 1 < p.nty) { wp[nw] = p.epoch + item + p.ntz; wn[nw++] = need; }
+                        if (tzi > 0) { wp[nw] = p.epoch + item - 1; wn[nw++] = need; }
+                        if (tzi + 1 < p.ntz) { wp[nw] = p.epoch + item + 1; wn[nw++] = need; }
+                    }
+                    const uint32_t needf = (uint32_t)n;
+                    const int nepoch = nw;
+                    if (chunk == 0 && p.flag_in[0]) { wp[nw] = p.flag_in[0]; wn[nw++] = needf; }
+                    if (chunk == p.nchunks - 1 && p.flag_in[1]) { wp[nw] = p.flag_in[1]; wn[nw++] = needf; }
+                    if (tyi == 0 && p.flag_in[2]) { wp[nw] = p.flag_in[2]; wn[nw++] = needf; }
+                    if (tyi == p.nty - 1 && p.flag_in[3]) { wp[nw] = p.flag_in[3]; wn[nw++] = needf; }
+                    if (tzi == 0 && p.flag_in[4]) { wp[nw] = p.flag_in[4]; wn[nw++] = needf; }
+                    if (tzi == p.ntz - 1 && p.flag_in[5]) { wp[nw] = p.flag_in[5]; wn[nw++] = needf; }
+                    if (nw) {
+                        for (;;) {
+                            bool ok = true;
+                            for (int q = 0; q < nw; q++)
+                                ok = ok && (*reinterpret_cast<const volatile uint32_t*>(wp[q]) >= wn[q]);
+                            if (ok) break;
+                            publish(false);  // never sit on finished items while waiting for somebody else's
+                            __nanosleep(32);
+                            if (globaltimer_ns() - t0 > p.timeout_ns) {
+                                atomicExch(&p.scratch[1], 1u);
+                                break;
+                            }
+                        }
+                        // acquire side: one gpu-scope fence for all epoch words (seven dependent acquire
+                        // loads cost ~5 us per item); the few rank-face items re-read their flag words with
+                        // a system-scope acquire load
+                        if (nepoch) __threadfence();
+                        for (int q = nepoch; q < nw; q++) (void)ld_acquire_sys(wp[q]);
+                    }
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                }
+                const CUtensorMap* msrc = &p.map_halo[w ^ 1];
+                const CUtensorMap* mio = &p.map_core[w];
                 const int c0_src = p.oz + k0 - 2, c1_src = j0;  // storage row(j0) - 1 == j0
                 const int c0_io = p.oz + k0, c1_io = j0 + 1;
                 for (int q = 0; q < nplanes + 2; q++) {
                     // source plane seq q = owned plane xa-1+q = storage plane xa+q
+                    publish(false);
                     mbar_wait(empty1 + 8u * s1i, ph1);
                     mbar_expect_tx(full1 + 8u * s1i, box1_bytes);
-                    tma_load_3d(ring1 + (uint32_t)s1i * slot1_bytes, &p.map_src, c0_src, c1_src, xa + q, full1 + 8u * s1i);
+                    tma_load_3d(ring1 + (uint32_t)s1i * slot1_bytes, msrc, c0_src, c1_src, xa + q, full1 + 8u * s1i);
                     if (++s1i == p.s1) { s1i = 0; ph1 ^= 1; }
                     if (!FIRST && q >= 2) {
                         // in-place plane of iteration q-2 = owned plane xa+q-2 = storage plane xa+q-1
                         mbar_wait(empty0 + 8u * s0i, ph0);
                         mbar_expect_tx(full0 + 8u * s0i, box0_bytes);
-                        tma_load_3d(ring0 + (uint32_t)s0i * slot0_bytes, &p.map_io, c0_io, c1_io, xa + q - 1, full0 + 8u * s0i);
+                        tma_load_3d(ring0 + (uint32_t)s0i * slot0_bytes, mio, c0_io, c1_io, xa + q - 1, full0 + 8u * s0i);
                         if (++s0i == p.s0) { s0i = 0; ph0 ^= 1; }
                     }
                 }
@@ -335,7 +463,8 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
         }
     } else {
         // ================================ compute warps ================================
-        const double cosn = s_bcast[0], rcos = s_bcast[1], coef = s_bcast[2];
+        double cosn = s_bcast[0], rcos = s_bcast[1];
+        const double coef = s_bcast[2];
         const double hx2 = p.hx2, hy2 = p.hy2, hz2 = p.hz2, rx = p.rx, ry = p.ry, rz = p.rz;
         const int64_t ps = p.ps;
         const bool xpush = (p.push_mask & 3u) != 0;
@@ -346,16 +475,29 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
         // ring cursors: F = next source plane to arrive, B = oldest source plane still held, F0 = in-place ring
         int fi = 0, bi = 0, f0i = 0;
         uint32_t fph = 0, f0ph = 0;
+        int cur_n = -1;
 
         for (int kq = 0;; kq++) {
             mbar_wait(ibar + 8u * (kq & 7), (uint32_t)((kq >> 3) & 1));
-            const int item = s_item[kq & 7];
-            if (item < 0) break;
+            const int gid = s_item[kq & 7];
+            if (gid < 0) break;
+            const int n = p.n0 + (MULTI ? gid / nitems : 0);
+            const int item = MULTI ? gid % nitems : gid;
+            const int w = n & 1;
             const int chunk = item / ntiles, tile = item - chunk * ntiles;
             const int xa = p.xcut[chunk];
             const int nplanes = p.xcut[chunk + 1] - xa;
             const int j0 = p.lo1 + (tile / p.ntz) * p.ty;
             const int k0 = p.lo2 + (tile % p.ntz) * kTZ;
+            double* const* dstw = p.dst[w];
+            if (MULTI && n != cur_n) {
+                // a new layer: its cosine, and fresh maxima (within a layer the running maxima and the
+                // rel-error filter threshold carry over from item to item; re-publishing a maximum is harmless)
+                cur_n = n;
+                cosn = cos(__fma_rn(__dmul_rn(p.a_t, (double)n), p.tau, p.twopi));
+                rcos = __ddiv_rn(1.0, fabs(cosn));
+                ea.mabs = ea.mrel = ea.best = ea.thr = 0.0;
+            }
 
             const int kk = k0 + 2 * lane;  // owned k of my first cell
             const bool vk0 = kk <= p.hi2, vk1 = kk + 1 <= p.hi2;
@@ -372,17 +514,17 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             double* zpb = nullptr;  // receives ub
             int64_t zsb = 0, zstep = 0;
             if ((p.push_mask & 16u) && kk == 0) {
-                zpa = p.dst[4] + xa * p.sa[4] + jr * p.sb[4];
+                zpa = dstw[4] + xa * p.sa[4] + jr * p.sb[4];
                 zsb = p.sb[4];
                 zstep = p.sa[4];
             }
             if (p.push_mask & 32u) {
                 if (kk == p.Z - 1) {
-                    zpa = p.dst[5] + xa * p.sa[5] + jr * p.sb[5];
+                    zpa = dstw[5] + xa * p.sa[5] + jr * p.sb[5];
                     zsb = p.sb[5];
                     zstep = p.sa[5];
                 } else if (kk + 1 == p.Z - 1) {
-                    zpb = p.dst[5] + xa * p.sa[5] + jr * p.sb[5];
+                    zpb = dstw[5] + xa * p.sa[5] + jr * p.sb[5];
                     zsb = p.sb[5];
                     zstep = p.sa[5];
                 }
@@ -393,15 +535,15 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                 vj[q] = j <= p.hi1 && vk0;
                 syq[q] = vj[q] ? p.sy[j] : 0.0;
                 rsyq[q] = vj[q] ? p.rsy[j] : 0.0;
-                orow[q] = p.out + (int64_t)(xa + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
+                orow[q] = p.field[w] + (int64_t)(xa + 1) * p.ps + (int64_t)(j + 1) * p.pitch + (p.oz + kk);
                 if (vj[q] && (p.push_mask & 4u) && j == 0) {
                     yq = q;
-                    yptr = p.dst[2] + xa * p.sa[2] + kk;
+                    yptr = dstw[2] + xa * p.sa[2] + kk;
                     ystep = p.sa[2];
                 }
                 if (vj[q] && (p.push_mask & 8u) && j == p.Y - 1) {
                     yq = q;
-                    yptr = p.dst[3] + xa * p.sa[3] + kk;
+                    yptr = dstw[3] + xa * p.sa[3] + kk;
                     ystep = p.sa[3];
                 }
             }
@@ -465,7 +607,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     if (vj[q]) {
                         if (vk1) *reinterpret_cast<double2*>(orow[q]) = make_double2(ua, ub);
                         else *orow[q] = ua;
-                        if (pslow) push_row_x(p, i, jr + q, kk, ua, ub, vk1);
+                        if (pslow) push_row_x(p, w, i, jr + q, kk, ua, ub, vk1);
                         if (q == yq) store_pair(yptr, ua, ub, vk1);
                         if (zany) {
                             if (zpa) zpa[q * zsb] = ua;
@@ -507,6 +649,22 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             }
             bi += 2;
             if (bi >= p.s1) bi -= p.s1;
+
+            if (MULTI) {
+                // ---- item complete: this layer's maxima, then hand the item to the producer lane
+                const double wa = warp_max(ea.mabs), wr = warp_max(ea.mrel);
+                if (lane == 0) {
+                    unsigned long long* e = reinterpret_cast<unsigned long long*>(p.err + 2 * (size_t)n);
+                    // thousands of items per layer share these two words: look before the atomic (same-address
+                    // atomics serialise in one L2 slice; after the first items hardly any maximum still grows)
+                    const unsigned long long ba = (unsigned long long)__double_as_longlong(wa);
+                    const unsigned long long br = (unsigned long long)__double_as_longlong(wr);
+                    if (wa > 0.0 && ba > *reinterpret_cast<volatile unsigned long long*>(e)) atomicMax(e, ba);
+                    if (wr > 0.0 && br > *reinterpret_cast<volatile unsigned long long*>(e + 1)) atomicMax(e + 1, br);
+                    mbar_arrive(pbar + 8u * (kq & 7));  // release at CTA scope; the producer lane publishes
+                }
+                __syncwarp();
+            }
         }
 
         if (dbg && tid == 0) g_dbg_ts[blockIdx.x * 8 + 3] = globaltimer_ns();
@@ -518,6 +676,17 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
         }
     }
     __syncthreads();  // also orders every thread's global / peer stores before thread 0's fence
+    if (MULTI) {
+        // the queue counter restarts when the last CTA leaves (everything else was published per item)
+        if (tid == 0) {
+            __threadfence();
+            if (atomicAdd(&p.scratch[0], 1u) == gridDim.x - 1) {
+                p.scratch[0] = 0;
+                p.scratch[2] = 0;
+            }
+        }
+        return;
+    }
     if (tid == 0) {
         if (dbg) g_dbg_ts[blockIdx.x * 8 + 4] = globaltimer_ns();
         double a = 0.0, r = 0.0;
@@ -525,8 +694,9 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             a = fmax(a, s_red[w][0]);
             r = fmax(r, s_red[w][1]);
         }
-        if (a > 0.0) atomicMax(reinterpret_cast<unsigned long long*>(p.err), (unsigned long long)__double_as_longlong(a));
-        if (r > 0.0) atomicMax(reinterpret_cast<unsigned long long*>(p.err + 1), (unsigned long long)__double_as_longlong(r));
+        unsigned long long* e = reinterpret_cast<unsigned long long*>(p.err + 2 * (size_t)p.n0);
+        if (a > 0.0) atomicMax(e, (unsigned long long)__double_as_longlong(a));
+        if (r > 0.0) atomicMax(e + 1, (unsigned long long)__double_as_longlong(r));
         // Order this CTA's stores (ghost cells in peer memory included: a store is performed at the
         // home L2 of its address) before the ticket. The gpu-scope fence is enough here: the last CTA
         // observes every ticket and its system-scope fence + release store make, by cumulativity, all
@@ -543,13 +713,13 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             p.scratch[0] = 0;
             p.scratch[2] = 0;  // every CTA has drawn its last (empty) item: the queue can restart
             if (p.root_err) {
-                const unsigned long long va = atomicMax(reinterpret_cast<unsigned long long*>(p.err), 0ull);
-                const unsigned long long vr = atomicMax(reinterpret_cast<unsigned long long*>(p.err + 1), 0ull);
-                atomicMax_system(reinterpret_cast<unsigned long long*>(p.root_err), va);
-                atomicMax_system(reinterpret_cast<unsigned long long*>(p.root_err + 1), vr);
+                const unsigned long long va = atomicMax(e, 0ull), vr = atomicMax(e + 1, 0ull);
+                unsigned long long* re = reinterpret_cast<unsigned long long*>(p.root_err + 2 * (size_t)p.n0);
+                atomicMax_system(re, va);
+                atomicMax_system(re + 1, vr);
             }
             for (int f = 0; f < 6; f++)
-                if (p.flag_out[f]) st_release_sys(p.flag_out[f], p.epoch_pub);
+                if (p.flag_out[f]) st_release_sys(p.flag_out[f], (uint32_t)p.n0 + 1u);
         }
     }
 }
@@ -780,23 +950,28 @@ int plan_smem_bytes(int ty, int tz, int s1, int s0) {
 
 typedef void (*StepKernel)(const StepParams);
 
+// mode: 0 = one layer (n >= 2), 1 = first layer (n == 1), 2 = multi-layer persistent launch
 template <int RJ>
-static StepKernel pick_rj(bool first, int div) {
-    switch ((first ? 4 : 0) + div) {
-        case 0: return k_step<RJ, false, 0>;
-        case 1: return k_step<RJ, false, 1>;
-        case 2: return k_step<RJ, false, 2>;
-        case 3: return k_step<RJ, false, 3>;
-        case 4: return k_step<RJ, true, 0>;
-        case 5: return k_step<RJ, true, 1>;
-        case 6: return k_step<RJ, true, 2>;
-        default: return k_step<RJ, true, 3>;
+static StepKernel pick_rj(int mode, int div) {
+    switch (mode * 4 + div) {
+        case 0: return k_step<RJ, false, 0, false>;
+        case 1: return k_step<RJ, false, 1, false>;
+        case 2: return k_step<RJ, false, 2, false>;
+        case 3: return k_step<RJ, false, 3, false>;
+        case 4: return k_step<RJ, true, 0, false>;
+        case 5: return k_step<RJ, true, 1, false>;
+        case 6: return k_step<RJ, true, 2, false>;
+        case 7: return k_step<RJ, true, 3, false>;
+        case 8: return k_step<RJ, false, 0, true>;
+        case 9: return k_step<RJ, false, 1, true>;
+        case 10: return k_step<RJ, false, 2, true>;
+        default: return k_step<RJ, false, 3, true>;
     }
 }
-static StepKernel pick_kernel(int rj, bool first, int div) {
-    if (rj == 1) return pick_rj<1>(first, div);
-    if (rj == 2) return pick_rj<2>(first, div);
-    return pick_rj<4>(first, div);
+static StepKernel pick_kernel(int rj, int mode, int div) {
+    if (rj == 1) return pick_rj<1>(mode, div);
+    if (rj == 2) return pick_rj<2>(mode, div);
+    return pick_rj<4>(mode, div);
 }
 
 // cudaFuncSetAttribute is per device; remember what was granted so that launches
@@ -816,13 +991,14 @@ static int ensure_smem_attr(const void* k, int smem) {
 }
 
 int prepare_step_kernels(const wave3d_plan* pl, int div) {
-    if (ensure_smem_attr((const void*)pick_kernel(pl->rj, false, div), plan_smem_bytes(pl->ty, pl->tz, pl->s1, pl->s0)))
-        return -1;
-    return ensure_smem_attr((const void*)pick_kernel(pl->rj, true, div), plan_smem_bytes(pl->ty, pl->tz, pl->s1, 0));
+    const int smem = plan_smem_bytes(pl->ty, pl->tz, pl->s1, pl->s0);
+    if (ensure_smem_attr((const void*)pick_kernel(pl->rj, 0, div), smem)) return -1;
+    if (ensure_smem_attr((const void*)pick_kernel(pl->rj, 2, div), smem)) return -1;
+    return ensure_smem_attr((const void*)pick_kernel(pl->rj, 1, div), plan_smem_bytes(pl->ty, pl->tz, pl->s1, 0));
 }
 
 int step_occupancy(int rj, int warps, int smem_bytes) {
-    StepKernel k = pick_kernel(rj, false, 0);
+    StepKernel k = pick_kernel(rj, 2, 0);  // the multi-layer variant needs the most registers
     if (cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes) != cudaSuccess) {
         cudaGetLastError();
         return 0;
@@ -849,23 +1025,38 @@ int launch_step(const StepLaunch& a) {
         set_last_error("invalid tile plan");
         return -1;
     }
+    const bool multi = a.nsteps > 1;
+    if (multi && (a.first || a.n < 2 || !a.epoch || !a.stepdone || a.desc)) {
+        set_last_error("multi-layer launch needs n >= 2, epoch/stepdone arrays and no step descriptor");
+        return -1;
+    }
     StepParams p;
     memset(&p, 0, sizeof p);
-    p.map_src = a.map_src;
-    p.map_io = a.map_io;
-    p.out = a.u_io;
+    for (int w = 0; w < 2; w++) {
+        p.map_halo[w] = a.map_halo[w];
+        p.map_core[w] = a.map_core[w];
+        p.field[w] = a.field[w];
+        for (int f = 0; f < 6; f++) p.dst[w][f] = a.peers[w].dst[f];
+    }
     p.sx = a.tabs[0]; p.sy = a.tabs[1]; p.sz = a.tabs[2];
     p.rsx = a.tabs[3]; p.rsy = a.tabs[4]; p.rsz = a.tabs[5];
+    const wave3d_peers& pw = a.peers[a.n & 1];
     for (int f = 0; f < 6; f++) {
-        p.dst[f] = a.peers.dst[f];
-        p.sa[f] = a.peers.sa[f];
-        p.sb[f] = a.peers.sb[f];
-        p.flag_out[f] = a.peers.flag_out[f];
-        p.flag_in[f] = a.peers.flag_in[f];
-        if (p.dst[f]) p.push_mask |= 1u << f;
+        p.sa[f] = pw.sa[f];
+        p.sb[f] = pw.sb[f];
+        p.flag_out[f] = pw.flag_out[f];
+        p.flag_in[f] = pw.flag_in[f];
+        if (pw.dst[f]) p.push_mask |= 1u << f;
     }
-    p.err = a.err + 2 * (size_t)a.n;
-    p.root_err = a.peers.root_err ? a.peers.root_err + 2 * (size_t)a.n : nullptr;
+    p.err = a.err;
+    p.root_err = pw.root_err;
+    p.epoch = a.epoch;
+    p.stepdone = a.stepdone;
+    p.n0 = a.n;
+    p.nsteps = multi ? a.nsteps : 1;
+    p.a_t = pr->a_t;
+    p.tau = pr->tau;
+    p.twopi = pr->pi + pr->pi;
     p.scratch = a.scratch;
     p.desc = a.desc;
     p.ps = l->plane_stride;
@@ -884,8 +1075,6 @@ int launch_step(const StepLaunch& a) {
     for (int c = 0; c <= pl->nchunks; c++) p.xcut[c] = pl->xcut[c];
     p.s1 = pl->s1; p.s0 = pl->s0;
     p.send_x0 = b->send_x[0]; p.send_x1 = b->send_x[1];
-    p.epoch_wait = (uint32_t)a.n;       // neighbours published layer n-1 as epoch n
-    p.epoch_pub = (uint32_t)a.n + 1u;
     {
         bool peers = p.push_mask != 0 || p.root_err != nullptr;
         for (int f = 0; f < 6; f++) peers = peers || p.flag_out[f] != nullptr;
@@ -894,11 +1083,18 @@ int launch_step(const StepLaunch& a) {
         if (const char* e = getenv("WAVE3D_DBG_TS")) p.dbg = atoi(e);
     }
     const int div = a.div_mode >= 0 ? a.div_mode : choose_div_mode(pr);
-    StepKernel k = pick_kernel(pl->rj, a.first != 0, div);
+    StepKernel k = pick_kernel(pl->rj, multi ? 2 : (a.first ? 1 : 0), div);
     const int smem = plan_smem_bytes(pl->ty, pl->tz, pl->s1, a.first ? 0 : pl->s0);
     if (ensure_smem_attr((const void*)k, smem)) return -1;
-    const int grid = pl->ctas;  // persistent CTAs; items (tile, x-chunk) are dealt out round-robin
-    k<<<grid, (pl->warps + 1) * 32, smem, a.stream>>>(p);  // + the TMA producer warp
+    const int grid = pl->ctas;  // persistent CTAs pulling (tile, x-chunk) items from the device-side queue
+    const int block = (pl->warps + 1) * 32;  // + the TMA producer warp
+    if (multi) {
+        // items wait on each other inside the kernel: every CTA must be resident
+        void* args[1] = {&p};
+        W3D_TRY(cudaLaunchCooperativeKernel((const void*)k, dim3(grid), dim3(block), args, (size_t)smem, a.stream));
+    } else {
+        k<<<grid, block, smem, a.stream>>>(p);
+    }
     W3D_TRY(cudaGetLastError());
     return 0;
 }
@@ -1036,12 +1232,15 @@ int wave3d_cuda_step(const wave3d_problem* p, const wave3d_box* b, const wave3d_
                      void* stream) {
     StepLaunch a;
     memset(&a, 0, sizeof a);
-    if (encode_field_map(&a.map_src, u1, l, plan->tz + 4, plan->ty + 2)) return -1;
-    if (encode_field_map(&a.map_io, u_io, l, plan->tz, plan->ty)) return -1;
+    const int w = n & 1;  // the layer being written plays the role of field n & 1
+    if (encode_field_map(&a.map_halo[w ^ 1], u1, l, plan->tz + 4, plan->ty + 2)) return -1;
+    if (encode_field_map(&a.map_core[w], u_io, l, plan->tz, plan->ty)) return -1;
+    a.field[w] = u_io;
+    a.field[w ^ 1] = const_cast<double*>(u1);
     a.prob = p; a.box = b; a.lay = l; a.plan = plan;
     for (int i = 0; i < 6; i++) a.tabs[i] = tabs[i];
-    a.u_io = u_io; a.n = n; a.first = first;
-    if (peers) a.peers = *peers;
+    a.n = n; a.nsteps = 1; a.first = first;
+    if (peers) a.peers[w] = *peers;
     a.err = err; a.scratch = scratch; a.spin_timeout_s = spin_timeout_s;
     a.div_mode = -1;
     a.stream = (cudaStream_t)stream;

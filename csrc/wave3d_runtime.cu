@@ -37,7 +37,10 @@ struct Rank {
     unsigned char* slab = nullptr;
     size_t slab_bytes = 0;
     size_t off_field[2] = {0, 0}, off_tabs[6] = {0}, off_err = 0, off_flags = 0, off_scratch = 0, off_desc = 0,
-           off_ferr = 0;
+           off_ferr = 0, off_epoch = 0, off_stepdone = 0;
+    size_t epoch_bytes = 0, stepdone_bytes = 0;
+    uint32_t* epoch = nullptr;     // multi-layer launch: last completed layer per (tile, chunk) item
+    uint32_t* stepdone = nullptr;  // multi-layer launch: completed items per layer
     double* field[2] = {nullptr, nullptr};
     double* tabs[6] = {nullptr};
     uint64_t* err = nullptr;
@@ -112,6 +115,12 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     off += align_up((size_t)(s->prob.timesteps + 1) * 16, 256);
     r.off_ferr = off;
     off += align_up((size_t)wave3d_cuda_field_error_scratch_words(&r.box) * 8 + 16, 256);
+    r.off_epoch = off;
+    r.epoch_bytes = align_up((size_t)r.plan.nty * r.plan.ntz * r.plan.nchunks * 4, 256);
+    off += r.epoch_bytes;
+    r.off_stepdone = off;
+    r.stepdone_bytes = align_up((size_t)(s->prob.timesteps + 2) * 4, 256);
+    off += r.stepdone_bytes;
     r.slab_bytes = off;
     W3D_TRY(cudaMalloc(&r.slab, r.slab_bytes));
     W3D_TRY(cudaMemsetAsync(r.slab, 0, r.slab_bytes, stream_of(s, r)));
@@ -122,6 +131,8 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     r.flags = reinterpret_cast<uint32_t*>(r.slab + r.off_flags);
     r.scratch = reinterpret_cast<uint32_t*>(r.slab + r.off_scratch);
     r.desc = reinterpret_cast<double*>(r.slab + r.off_desc);
+    r.epoch = reinterpret_cast<uint32_t*>(r.slab + r.off_epoch);
+    r.stepdone = reinterpret_cast<uint32_t*>(r.slab + r.off_stepdone);
     for (int w = 0; w < 2; w++) {
         if (encode_field_map(&r.map_halo[w], r.field[w], &r.lay, r.plan.tz + 4, r.plan.ty + 2)) return -1;
         if (encode_field_map(&r.map_core[w], r.field[w], &r.lay, r.plan.tz, r.plan.ty)) return -1;
@@ -238,27 +249,35 @@ int enqueue_layer0_rank(wave3d_solver* s, Rank& r) {
     return 0;
 }
 
-int enqueue_step_rank(wave3d_solver* s, Rank& r, int n, const double* pinned_desc) {
-    if (use_device(r.device)) return -1;
-    StepLaunch a;
+void fill_launch(wave3d_solver* s, Rank& r, StepLaunch& a) {
     memset(&a, 0, sizeof a);
-    const int w = n & 1;  // layer n is written into field n&1, source is the other field
-    a.map_src = r.map_halo[w ^ 1];
-    a.map_io = r.map_core[w];
+    for (int w = 0; w < 2; w++) {
+        a.map_halo[w] = r.map_halo[w];
+        a.map_core[w] = r.map_core[w];
+        a.field[w] = r.field[w];
+        if (s->opts.transport == WAVE3D_TRANSPORT_PEER && s->connected) a.peers[w] = r.peers[w];
+    }
     a.prob = &s->prob;
     a.box = &r.box;
     a.lay = &r.lay;
     a.plan = &r.plan;
     for (int t = 0; t < 6; t++) a.tabs[t] = r.tabs[t];
-    a.u_io = r.field[w];
-    a.n = n;
-    a.first = n == 1;
-    if (s->opts.transport == WAVE3D_TRANSPORT_PEER && s->connected) a.peers = r.peers[w];
     a.err = r.err;
     a.scratch = r.scratch;
+    a.epoch = r.epoch;
+    a.stepdone = r.stepdone;
     a.spin_timeout_s = s->opts.spin_timeout_s;
     a.div_mode = s->div_mode;
     a.stream = stream_of(s, r);
+}
+
+int enqueue_step_rank(wave3d_solver* s, Rank& r, int n, const double* pinned_desc) {
+    if (use_device(r.device)) return -1;
+    StepLaunch a;
+    fill_launch(s, r, a);  // layer n is written into field n&1, the source is the other field
+    a.n = n;
+    a.nsteps = 1;
+    a.first = n == 1;
     if (pinned_desc) {  // end-to-end mode: this step's inputs arrive from pinned host memory
         W3D_TRY(cudaMemcpyAsync(r.desc + 2 * n, pinned_desc, 16, cudaMemcpyHostToDevice, a.stream));
         a.desc = r.desc + 2 * n;
@@ -270,6 +289,39 @@ int enqueue_step_rank(wave3d_solver* s, Rank& r, int n, const double* pinned_des
         s->launches++;
     }
     return 0;
+}
+
+// Layers n0 .. timesteps of one rank in a single persistent cooperative launch (k_step<..., MULTI>).
+int enqueue_multi_rank(wave3d_solver* s, Rank& r, int n0) {
+    if (use_device(r.device)) return -1;
+    StepLaunch a;
+    fill_launch(s, r, a);
+    a.n = n0;
+    a.nsteps = s->prob.timesteps - n0 + 1;
+    a.first = 0;
+    if (launch_step(a)) return -1;
+    s->launches++;
+    return 0;
+}
+
+// The multi-layer launch keeps a rank's kernel resident across layers while it waits for its
+// neighbours' flags, so it needs the GPU for itself: one local rank per device.
+bool multistep_ok(const wave3d_solver* s) {
+    if (!s->opts.multistep || s->opts.backend != WAVE3D_BACKEND_CUDA) return false;
+    if (s->opts.transport != WAVE3D_TRANSPORT_PEER || s->opts.per_step_sync) return false;
+    if (s->prob.timesteps < 3) return false;
+    for (auto& g : s->groups)
+        if (g.members.size() != 1) return false;
+    if (const char* e = getenv("WAVE3D_MULTISTEP")) {
+        if (!strcmp(e, "0")) return false;
+        if (!strcmp(e, "1")) return true;
+    }
+    // Measured on B200: below ~50 M cells per rank the launch gap, pipeline fill and kernel tail of
+    // one launch per layer dominate (N=256: 162 -> 191 Gcell/s in one launch); above it the lock-step
+    // start of every layer is worth more (N=512: 250 vs 240).
+    for (auto& r : s->ranks)
+        if ((double)r.box.n[0] * r.box.n[1] * r.box.n[2] > 48e6) return false;
+    return true;
 }
 
 }  // namespace
@@ -325,7 +377,8 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
             // guided chunk lengths: start near 60 % of a CTA's share (never more than half a column),
             // halve down to a floor that bounds the end-of-kernel imbalance
             const double share = (double)ntiles * X / ctas;
-            const int minlen = std::max(4, std::min(X, std::max(8, X / 32)));
+            int minlen = std::max(4, std::min(X, std::max(8, X / 32)));
+            if (const char* e = getenv("WAVE3D_MINLEN")) minlen = std::max(2, std::min(X, atoi(e)));
             int cuts[18];
             int m = 0;
             cuts[0] = 0;
@@ -379,6 +432,7 @@ void wave3d_solver_opts_default(wave3d_solver_opts* o) {
     o->nlocal = 1;
     for (int i = 0; i < 8; i++) o->devices[i] = -1;
     o->use_graph = 1;
+    o->multistep = 1;
     o->spin_timeout_s = 10.0;
 }
 
@@ -618,6 +672,7 @@ int wave3d_solver_reset(wave3d_solver* s) {
         W3D_TRY(cudaMemsetAsync(r.err, 0, (size_t)(s->prob.timesteps + 1) * 16, st));
         W3D_TRY(cudaMemsetAsync(r.flags, 0, 256, st));
         W3D_TRY(cudaMemsetAsync(r.scratch, 0, 256, st));
+        W3D_TRY(cudaMemsetAsync(r.epoch, 0, r.epoch_bytes + r.stepdone_bytes, st));
     }
     s->fresh = true;
     return wave3d_solver_sync(s);
@@ -813,7 +868,12 @@ static int enqueue_all(wave3d_solver* s, Group* only) {
     };
     if (members([&](Rank& r) { return enqueue_layer0_rank(s, r); })) return -1;
     if (staged && wave3d_solver_exchange_local(s, 0)) return -1;
+    const bool multi = multistep_ok(s);
     for (int n = 1; n <= s->prob.timesteps; n++) {
+        if (multi && n == 2) {
+            if (members([&](Rank& r) { return enqueue_multi_rank(s, r, 2); })) return -1;
+            break;
+        }
         if (members([&](Rank& r) { return enqueue_step_rank(s, r, n, nullptr); })) return -1;
         if (staged && n < s->prob.timesteps && wave3d_solver_exchange_local(s, n)) return -1;
     }
@@ -849,7 +909,8 @@ int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
         return -1;
     }
     const bool per_step = s->opts.per_step_sync != 0;
-    const bool graph = s->opts.use_graph && !per_step && !staged;
+    // the multi-layer path is a handful of launches: nothing for a graph to save
+    const bool graph = s->opts.use_graph && !per_step && !staged && !multistep_ok(s);
     if (graph) {
         for (auto& g : s->groups) {
             if (g.exec) continue;

@@ -292,6 +292,8 @@ typedef struct wave3d_solver_opts {
     int32_t threads;       /* CPU backend threads */
     int32_t per_step_sync; /* read the step's error maxima back after every step (e2e / progress mode) */
     int32_t verbose;
+    int32_t multistep;     /* layers 2..timesteps in ONE persistent dataflow launch per GPU (default 1; needs one rank per GPU) */
+    int32_t reserved;
     double spin_timeout_s; /* bound on in-kernel flag waits; <=0 -> 10 s */
 } wave3d_solver_opts;
 
