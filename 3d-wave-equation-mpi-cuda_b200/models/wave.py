@@ -208,7 +208,8 @@ class WaveSolver:
         a, r = self.errors()
         return SolveResult(a, r, t.solve_ms, self.init_ms, self.launches - before, self.nranks, self.dims,
                            self.problem.cells, self.problem.timesteps,
-                           {"plan": self.plan(0).as_dict() if self.backend == "cuda" else None})
+                           {"plan": self.plan(0).as_dict() if self.backend == "cuda" else None,
+                            "exchange_ms": t.exchange_ms, "loop_ms": t.loop_ms})
 
     solve = run
 
@@ -241,6 +242,7 @@ class WaveSolver:
     # --------------------------------------------------------------- report
     def report(self, res: SolveResult, precision: int = 0) -> str:
         return _report.format_report(self.problem, res.max_abs, res.max_rel, res.solve_ms, res.init_ms,
+                                     loop_ms=res.extra.get("loop_ms"), exchange_ms=res.extra.get("exchange_ms", 0.0),
                                      precision=precision, cuda_style=self.backend == "cuda")
 
     def write_report(self, res: SolveResult, path: Optional[str] = None, precision: int = 0) -> str:

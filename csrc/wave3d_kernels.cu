@@ -559,10 +559,10 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             uint32_t ac = ring1 + (uint32_t)fi * slot1_bytes;
             if (++fi == p.s1) { fi = 0; fph ^= 1; }
 
+            if (dbg && tid == 0 && kq == 0) g_dbg_ts[blockIdx.x * 8 + 2] = globaltimer_ns();  // first data is here
             for (int t = 0; t < nplanes; t++) {
                 const int i = xa + t;  // owned x index of the centre plane
                 mbar_wait(full1 + 8u * fi, fph);
-                if (dbg && tid == 0 && t == 0 && kq == 0) g_dbg_ts[blockIdx.x * 8 + 2] = globaltimer_ns();
                 const uint32_t ap = ring1 + (uint32_t)fi * slot1_bytes;
                 if (++fi == p.s1) { fi = 0; fph ^= 1; }
                 uint32_t a0 = 0;

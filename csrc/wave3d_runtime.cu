@@ -84,6 +84,8 @@ struct wave3d_solver {
     int64_t launches = 0;
     double* pinned = nullptr;  // 2 doubles per layer per local rank (per-step readback) + descriptors
     double exchange_ms = 0.0;
+    std::vector<cudaEvent_t> xev;  // event pairs around staged exchanges
+    int xev_used = 0;
     bool fresh = false;  // reset() was called and nothing ran since
 };
 
@@ -458,6 +460,7 @@ void wave3d_solver_destroy(wave3d_solver* s) {
             if (r.ev_unpacked) cudaEventDestroy(r.ev_unpacked);
             if (r.slab) cudaFree(r.slab);
         }
+        for (cudaEvent_t e : s->xev) cudaEventDestroy(e);
         if (s->pinned) cudaFreeHost(s->pinned);
         cudaGetLastError();
     }
@@ -857,6 +860,25 @@ int wave3d_solver_status(wave3d_solver* s) {
 
 // Enqueue the whole solve for one device group, layer by layer, ranks interleaved so
 // that ranks sharing a device never wait on a kernel queued behind them.
+static int timed_exchange(wave3d_solver* s, int n) {
+    // staged transport: bracket every exchange with an event pair on the first device's stream; the
+    // pairs are read after the solve, so nothing here blocks the host (ref: total_exchange_time /
+    // total_mpi_exchange_time, cuda_sol.cpp:235-243,291-304)
+    Group& g = s->groups[0];
+    if (use_device(g.device)) return -1;
+    while (s->xev.size() < 2 * (size_t)(s->xev_used + 1)) {
+        cudaEvent_t e;
+        W3D_TRY(cudaEventCreate(&e));
+        s->xev.push_back(e);
+    }
+    W3D_TRY(cudaEventRecord(s->xev[2 * s->xev_used], g.stream));
+    if (wave3d_solver_exchange_local(s, n)) return -1;
+    if (use_device(g.device)) return -1;
+    W3D_TRY(cudaEventRecord(s->xev[2 * s->xev_used + 1], g.stream));
+    s->xev_used++;
+    return 0;
+}
+
 static int enqueue_all(wave3d_solver* s, Group* only) {
     const bool staged = s->opts.transport == WAVE3D_TRANSPORT_STAGED;
     auto members = [&](auto fn) -> int {
@@ -867,7 +889,7 @@ static int enqueue_all(wave3d_solver* s, Group* only) {
         return 0;
     };
     if (members([&](Rank& r) { return enqueue_layer0_rank(s, r); })) return -1;
-    if (staged && wave3d_solver_exchange_local(s, 0)) return -1;
+    if (staged && timed_exchange(s, 0)) return -1;
     const bool multi = multistep_ok(s);
     for (int n = 1; n <= s->prob.timesteps; n++) {
         if (multi && n == 2) {
@@ -875,7 +897,7 @@ static int enqueue_all(wave3d_solver* s, Group* only) {
             break;
         }
         if (members([&](Rank& r) { return enqueue_step_rank(s, r, n, nullptr); })) return -1;
-        if (staged && n < s->prob.timesteps && wave3d_solver_exchange_local(s, n)) return -1;
+        if (staged && n < s->prob.timesteps && timed_exchange(s, n)) return -1;
     }
     return 0;
 }
@@ -886,6 +908,8 @@ int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
     // late flag must not be wiped, an early one must not be lost); otherwise reset here.
     if (!s->fresh && wave3d_solver_reset(s)) return -1;
     s->fresh = false;
+    s->exchange_ms = 0.0;
+    s->xev_used = 0;
     if (s->opts.backend != WAVE3D_BACKEND_CUDA) {
         if (!s->all_local) return -1;
         auto t0 = std::chrono::steady_clock::now();
@@ -961,9 +985,15 @@ int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
         W3D_TRY(cudaEventElapsedTime(&ms, g.ev0, g.ev1));
         if (ms > solve) solve = ms;  // max over the devices driven by this process
     }
+    if (s->xev_used) use_device(s->groups[0].device);
+    for (int i = 0; i < s->xev_used; i++) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s->xev[2 * i], s->xev[2 * i + 1]) == cudaSuccess) s->exchange_ms += ms;
+    }
     if (t) {
         t->solve_ms = solve;
-        t->loop_ms = solve;
+        t->exchange_ms = s->exchange_ms;
+        t->loop_ms = solve - s->exchange_ms;
     }
     if (wave3d_solver_status(s) != 0) {
         set_last_error("in-kernel halo wait timed out (a neighbour rank did not publish its layer)");
@@ -1013,8 +1043,10 @@ int wave3d_main(int argc, const char* const* argv) {
     if (o.backend == WAVE3D_BACKEND_CUDA) {
         char host[256] = "localhost";
         gethostname(host, sizeof host);
+        // ref: cuda_sol.cpp:513 prints this line from every MPI rank; here all ranks live in this process
+        for (int r = 0; r < nranks; r++)
+            printf("Process %d local rank = %d local size = %d hostname = %s (GPU %d)\n", r, r, nranks, host, r % ndev);
         printf("number of CUDA devices on node %s: %d\n", host, ndev);  // ref: cuda_sol.cpp:531
-        for (int r = 0; r < nranks; r++) printf("rank %d -> GPU %d\n", r, r % ndev);
     }
     auto t0 = std::chrono::steady_clock::now();
     wave3d_solver* s = wave3d_solver_create(&p, &o, err, sizeof err);
@@ -1058,6 +1090,8 @@ int wave3d_main(int argc, const char* const* argv) {
     const int cuda_style = o.backend == WAVE3D_BACKEND_CUDA;
     char name[256];
     wave3d_output_name(p.N, p.Np, 0, name, sizeof name);
+    if (const char* e = getenv("WAVE3D_NAME_STYLE"))  // "cuda": the MPI+CUDA program's own name (ref: cuda_sol.cpp:535)
+        if (!strcmp(e, "cuda")) wave3d_output_name(p.N, nranks, ndev > 0 ? ndev : 1, name, sizeof name);
     if (const char* e = getenv("WAVE3D_OUTPUT")) snprintf(name, sizeof name, "%s", e);
     std::vector<char> buf(wave3d_format_report(&p, &tm, ea.data(), er.data(), 0, cuda_style, nullptr, 0));
     wave3d_format_report(&p, &tm, ea.data(), er.data(), 0, cuda_style, buf.data(), buf.size());

@@ -154,3 +154,13 @@ def test_multistep_dataflow_launch_equals_per_step_launches(N, lengths, monkeypa
         assert b1.launches < a.launches
     assert a.max_abs == b1.max_abs == b2.max_abs
     assert a.max_rel == b1.max_rel == b2.max_rel
+
+
+def test_staged_transport_reports_exchange_time():
+    p = w.Problem(N=48, T=0.05, timesteps=5)
+    with w.WaveSolver(p, nranks=2, backend="cuda", devices=[0], transport="staged") as s:
+        res = s.run()
+        txt = s.report(res)
+    assert res.extra["exchange_ms"] > 0.0 and res.extra["loop_ms"] < res.solve_ms
+    line = [l for l in txt.splitlines() if l.startswith("total MPI exchange time:")][0]
+    assert float(line.split()[-2]) > 0.0
