@@ -213,6 +213,30 @@ class WaveSolver:
 
     solve = run
 
+    def make_descriptors(self):
+        """Pinned host tensor [timesteps+1, 2] with every layer's step inputs (time argument, coefficient)."""
+        import torch
+        d = torch.zeros((self.problem.timesteps + 1, 2), dtype=torch.float64).pin_memory()
+        for n in range(1, self.problem.timesteps + 1):
+            d[n, 0], d[n, 1] = self.step_descriptor(n)
+        return d
+
+    def run_streamed(self, desc=None, lag: int = 1) -> SolveResult:
+        """End-to-end solve through the per-step path: every layer's inputs are copied from pinned host
+        memory, every layer's maxima are read back to the host while the solve runs (``lag`` layers behind
+        the device; 0 = wait for each layer before launching the next, like the reference). Wall-clock timed."""
+        if desc is None:
+            desc = self.make_descriptors()
+        L = self.problem.timesteps + 1
+        out = (C.c_double * (2 * L))()
+        t = _lib.Timings()
+        before = self.launches
+        rc = _lib.lib().wave3d_solver_run_streamed(self._h, desc.data_ptr(), lag, out, C.byref(t))
+        self._chk(rc, "solver_run_streamed")
+        return SolveResult([out[2 * n] for n in range(L)], [out[2 * n + 1] for n in range(L)], t.solve_ms, self.init_ms,
+                           self.launches - before, self.nranks, self.dims, self.problem.cells, self.problem.timesteps,
+                           {"h2d_bytes_per_step": 16 * self.nlocal, "d2h_bytes_per_step": 16 * self.nlocal, "lag": lag})
+
     def run_per_step(self, progress=None) -> SolveResult:
         """Reference-style driver: after every layer the maxima are read back to the host
         (what cuda_sol does with 'calculating layer n' + calculate_errors every step)."""

@@ -109,38 +109,37 @@ def run_ours(a):
     # ---- end to end through the public per-step API: every step uploads its descriptor from pinned host
     # memory (H2D), runs the fused kernel, and reads the step's error maxima back (D2H) before the next step
     e2e = None
-    if not a.no_e2e:
-        desc = torch.empty((K + 1, 2), dtype=torch.float64).pin_memory()
-        for n in range(1, K + 1):
-            desc[n, 0], desc[n, 1] = inner.step_descriptor(n)
-        e2e_times = []
-        for rep in range(3):
+    if not a.no_e2e and transport == "peer":
+        # WaveSolver.run_streamed: per layer H2D of the step descriptor (pinned), fused kernel, D2H of the
+        # layer's maxima; the host reads layer n while layer n+1 runs (lag 1). lag 0 = wait for every layer.
+        desc = inner.make_descriptors()
+        def streamed(lag):
+            ts = []
+            for rep in range(3):
+                if distributed:
+                    solver._reset()
+                else:
+                    solver.reset()
+                barrier()
+                r = inner.run_streamed(desc, lag=lag)
+                barrier()
+                ts.append(r.solve_ms)
+            t = statistics.median(ts[1:])
             if distributed:
-                solver._reset()
-            else:
-                solver.reset()
-            barrier()
-            t0 = time.perf_counter()
-            inner.enqueue_layer0()
-            if transport == "staged":
-                (solver.halo.exchange(0) if distributed else inner.exchange_local(0))
-            errs = []
-            for n in range(1, K + 1):
-                inner.enqueue_step_e2e(n, desc[n].data_ptr())
-                if transport == "staged" and n < K:
-                    (solver.halo.exchange(n) if distributed else inner.exchange_local(n))
-                errs.append(inner.layer_error(n))
-            barrier()
-            e2e_times.append((time.perf_counter() - t0) * 1e3)
-        t_e2e = statistics.median(e2e_times[1:]) if len(e2e_times) > 1 else e2e_times[0]
-        if distributed:
-            tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            t_e2e = float(tt.item())
+                tt = torch.tensor([t], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                t = float(tt.item())
+            return t, r
+        t_e2e, r_e2e = streamed(1)
+        t_sync, _ = streamed(0)
+        assert r_e2e.max_abs[-1] == res.max_abs[-1] or distributed  # same solve (local maxima under torchrun)
         e2e = {"value": cells * K / (t_e2e * 1e-3) / 1e9, "unit": "Gcell-updates/s", "h2d_bytes_per_step": 16,
-               "d2h_bytes_per_step": 16, "ms_per_step": t_e2e / K,
-               "note": "per step: pinned->device copy of the step descriptor, fused kernel, device->host read of "
-                       "the step's max abs/rel error, stream sync; wall clock, max over ranks"}
+               "d2h_bytes_per_step": 16, "ms_per_step": t_e2e / K, "lag_layers": 1,
+               "sync_value": cells * K / (t_sync * 1e-3) / 1e9,
+               "note": "WaveSolver.run_streamed: every layer copies its step descriptor pinned->device, runs the fused "
+                       "kernel and copies its max abs/rel error device->host; the host reads layer n while layer n+1 "
+                       "runs (sync_value: host waits for every layer before launching the next). Wall clock incl. "
+                       "layer 0, max over ranks; bytes are per rank"}
     # roofline: 24 B of HBM traffic per cell per step (read u^{n-1}, read u^{n-2}, write u^n) against the
     # MEASURED copy bandwidth of this pool (MEASURED_PEAKS.json; fallback 6650 GB/s, B200_PROFILING.md)
     hbm, src = 6650.0, "fallback"

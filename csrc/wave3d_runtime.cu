@@ -85,6 +85,7 @@ struct wave3d_solver {
     double* pinned = nullptr;  // 2 doubles per layer per local rank (per-step readback) + descriptors
     double exchange_ms = 0.0;
     std::vector<cudaEvent_t> xev;  // event pairs around staged exchanges
+    std::vector<cudaEvent_t> sev;  // streamed solve: per layer, per device group
     int xev_used = 0;
     bool fresh = false;  // reset() was called and nothing ran since
 };
@@ -461,6 +462,7 @@ void wave3d_solver_destroy(wave3d_solver* s) {
             if (r.slab) cudaFree(r.slab);
         }
         for (cudaEvent_t e : s->xev) cudaEventDestroy(e);
+        for (cudaEvent_t e : s->sev) cudaEventDestroy(e);
         if (s->pinned) cudaFreeHost(s->pinned);
         cudaGetLastError();
     }
@@ -841,6 +843,70 @@ int wave3d_solver_errors(wave3d_solver* s, double* max_abs, double* max_rel) {
         max_rel[n] = r_;
     }
     return 0;
+}
+
+int wave3d_solver_run_streamed(wave3d_solver* s, const double* pinned_desc, int lag, double* abs_rel,
+                               wave3d_timings* t) {
+    if (!s || s->opts.backend != WAVE3D_BACKEND_CUDA || !pinned_desc || !abs_rel) return -1;
+    const int T = s->prob.timesteps, L = (int)s->ranks.size();
+    if (lag < 0) lag = 0;
+    const bool staged = s->opts.transport == WAVE3D_TRANSPORT_STAGED;
+    if (staged && !s->all_local) {
+        set_last_error("streamed solve with the staged transport across processes is driven by the caller");
+        return -1;
+    }
+    if (!s->fresh && wave3d_solver_reset(s)) return -1;
+    s->fresh = false;
+    // one event per layer per device group marks "this layer's maxima are in pinned memory"
+    while (s->sev.size() < (size_t)(T + 1) * s->groups.size()) {
+        cudaEvent_t e;
+        if (use_device(s->groups[s->sev.size() % s->groups.size()].device)) return -1;
+        W3D_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        s->sev.push_back(e);
+    }
+    for (int i = 0; i < 2 * (T + 1); i++) abs_rel[i] = 0.0;
+    auto collect = [&](int n) -> int {
+        for (size_t g = 0; g < s->groups.size(); g++) {
+            if (use_device(s->groups[g].device)) return -1;
+            W3D_TRY(cudaEventSynchronize(s->sev[(size_t)n * s->groups.size() + g]));
+        }
+        for (auto& r : s->ranks) {
+            const double* src = s->pinned + 2 * ((size_t)n * L + r.local);
+            r.habs[n] = src[0];
+            r.hrel[n] = src[1];
+            if (src[0] > abs_rel[2 * n]) abs_rel[2 * n] = src[0];
+            if (src[1] > abs_rel[2 * n + 1]) abs_rel[2 * n + 1] = src[1];
+        }
+        return 0;
+    };
+    auto t0 = std::chrono::steady_clock::now();
+    for (auto& r : s->ranks)
+        if (enqueue_layer0_rank(s, r)) return -1;
+    if (staged && wave3d_solver_exchange_local(s, 0)) return -1;
+    for (int n = 1; n <= T; n++) {
+        for (auto& r : s->ranks)
+            if (enqueue_step_rank(s, r, n, pinned_desc + 2 * n)) return -1;
+        if (staged && n < T && wave3d_solver_exchange_local(s, n)) return -1;
+        for (auto& r : s->ranks) {
+            if (use_device(r.device)) return -1;
+            W3D_TRY(cudaMemcpyAsync(s->pinned + 2 * ((size_t)n * L + r.local), r.err + 2 * n, 16, cudaMemcpyDeviceToHost,
+                                    stream_of(s, r)));
+        }
+        for (size_t g = 0; g < s->groups.size(); g++) {
+            if (use_device(s->groups[g].device)) return -1;
+            W3D_TRY(cudaEventRecord(s->sev[(size_t)n * s->groups.size() + g], s->groups[g].stream));
+        }
+        if (n - lag >= 1 && collect(n - lag)) return -1;
+    }
+    for (int n = std::max(1, T - lag + 1); n <= T; n++)
+        if (collect(n)) return -1;
+    if (wave3d_solver_sync(s)) return -1;
+    auto t1 = std::chrono::steady_clock::now();
+    if (t) {
+        memset(t, 0, sizeof *t);
+        t->solve_ms = t->loop_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    }
+    return wave3d_solver_status(s) ? -2 : 0;
 }
 
 int64_t wave3d_solver_kernel_launches(const wave3d_solver* s) { return s ? s->launches : 0; }

@@ -350,6 +350,14 @@ int wave3d_solver_sync(wave3d_solver* s);
  * process call it on every rank between two barriers. */
 int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t);
 
+/* Streamed solve = the end-to-end flavour of a whole solve through the per-step API: for every layer the
+ * step descriptor (wave3d_step_descriptor) is copied host->device from `pinned_desc` (2 doubles per layer,
+ * pinned host memory), the fused kernel runs, and the layer's two maxima are copied device->host. The host
+ * reads layer n's maxima before it enqueues layer n+1+lag (lag 0: fully synchronous, like the reference's
+ * per-layer error read-back; lag 1 hides the host round trip behind the next layer). abs_rel receives
+ * 2*(timesteps+1) doubles (max over the local ranks). solve_ms is host wall-clock time. */
+int wave3d_solver_run_streamed(wave3d_solver* s, const double* pinned_desc, int lag, double* abs_rel, wave3d_timings* t);
+
 /* Per-layer maxima over the local ranks (timesteps+1 entries each). */
 int wave3d_solver_errors(wave3d_solver* s, double* max_abs, double* max_rel);
 /* Error maxima of one layer, read back synchronously (per-step mode). */

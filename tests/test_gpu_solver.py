@@ -164,3 +164,13 @@ def test_staged_transport_reports_exchange_time():
     assert res.extra["exchange_ms"] > 0.0 and res.extra["loop_ms"] < res.solve_ms
     line = [l for l in txt.splitlines() if l.startswith("total MPI exchange time:")][0]
     assert float(line.split()[-2]) > 0.0
+
+
+@pytest.mark.parametrize("lag", [0, 1, 3])
+def test_streamed_solve_equals_batch_solve(lag):
+    p = w.Problem(N=56, Lx=1.0, Ly=2.0, Lz=3.0, T=0.05, timesteps=7)
+    with w.WaveSolver(p, nranks=2, backend="cuda", devices=[0]) as s:
+        ref = s.run()
+        got = s.run_streamed(lag=lag)
+    assert got.max_abs == ref.max_abs and got.max_rel == ref.max_rel
+    assert got.extra["h2d_bytes_per_step"] == 32 and got.solve_ms > 0
