@@ -50,11 +50,12 @@ class Plan(C.Structure):
     _fields_ = [("tz", C.c_int32), ("ty", C.c_int32), ("rj", C.c_int32), ("warps", C.c_int32),
                 ("nty", C.c_int32), ("ntz", C.c_int32), ("nchunks", C.c_int32), ("s1", C.c_int32), ("s0", C.c_int32),
                 ("smem_bytes", C.c_int32), ("ctas", C.c_int32), ("slots", C.c_int32), ("efficiency", C.c_double),
-                ("xcut", C.c_int32 * 18)]
+                ("xcut", C.c_int32 * 18), ("order", C.c_int32 * 16)]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "xcut"}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("xcut", "order")}
         d["xcut"] = list(self.xcut[:self.nchunks + 1])
+        d["order"] = list(self.order[:self.nchunks])
         return d
 
 

@@ -129,7 +129,10 @@ struct alignas(64) StepParams {
     int lo1, hi1, lo2, hi2;
     int elo0, ehi0;
     int nty, ntz, nchunks, ty, tz;
-    int xcut[18];
+    int xcut[18];        // x-chunk boundaries by POSITION along x
+    signed char pos_of[16];  // processing index (queue order within a layer) -> position
+    signed char pi_of[16];   // position -> processing index
+    int self_wrap;       // the x neighbours are this rank itself (periodic wrap inside one box)
     int s1, s0;
     int send_x0, send_x1;
     uint32_t push_mask;  // bit f set: dst[.][f] != nullptr
@@ -387,7 +390,8 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                 const int n = p.n0 + (MULTI ? gid / nitems : 0);
                 const int item = MULTI ? gid % nitems : gid;
                 const int w = n & 1;  // layer n is written into field w, the stencil source is field w^1
-                const int chunk = item / ntiles, tile = item - chunk * ntiles;
+                const int pidx = item / ntiles, tile = item - pidx * ntiles;
+                const int chunk = p.pos_of[pidx];  // position of the chunk along x
                 const int xa = p.xcut[chunk];
                 const int nplanes = p.xcut[chunk + 1] - xa;
                 const int tyi = tile / p.ntz, tzi = tile - tyi * p.ntz;
@@ -404,8 +408,15 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     if (n > p.n0) {
                         const uint32_t need = (uint32_t)(n - 1);
                         wp[nw] = p.epoch + item; wn[nw++] = need;
-                        if (chunk > 0) { wp[nw] = p.epoch + item - ntiles; wn[nw++] = need; }
-                        if (chunk + 1 < p.nchunks) { wp[nw] = p.epoch + item + ntiles; wn[nw++] = need; }
+                        // x neighbours by position; with the periodic wrap inside this box the two end
+                        // chunks of a tile column are neighbours too (ghost planes written by each other)
+                        int cm = chunk - 1, cp = chunk + 1;
+                        if (p.self_wrap) {
+                            if (cm < 0) cm = p.nchunks - 1;
+                            if (cp == p.nchunks) cp = 0;
+                        }
+                        if (cm >= 0 && cm != chunk) { wp[nw] = p.epoch + p.pi_of[cm] * ntiles + tile; wn[nw++] = need; }
+                        if (cp < p.nchunks && cp != chunk && cp != cm) { wp[nw] = p.epoch + p.pi_of[cp] * ntiles + tile; wn[nw++] = need; }
                         if (tyi > 0) { wp[nw] = p.epoch + item - p.ntz; wn[nw++] = need; }
                         if (tyi + 1 < p.nty) { wp[nw] = p.epoch + item + p.ntz; wn[nw++] = need; }
                         if (tzi > 0) { wp[nw] = p.epoch + item - 1; wn[nw++] = need; }
@@ -484,7 +495,8 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             const int n = p.n0 + (MULTI ? gid / nitems : 0);
             const int item = MULTI ? gid % nitems : gid;
             const int w = n & 1;
-            const int chunk = item / ntiles, tile = item - chunk * ntiles;
+            const int pidx = item / ntiles, tile = item - pidx * ntiles;
+            const int chunk = p.pos_of[pidx];
             const int xa = p.xcut[chunk];
             const int nplanes = p.xcut[chunk + 1] - xa;
             const int j0 = p.lo1 + (tile / p.ntz) * p.ty;
@@ -1025,6 +1037,15 @@ int launch_step(const StepLaunch& a) {
         set_last_error("invalid tile plan");
         return -1;
     }
+    {
+        int seen = 0;
+        for (int c = 0; c < pl->nchunks; c++)
+            if (pl->order[c] >= 0 && pl->order[c] < pl->nchunks) seen |= 1 << pl->order[c];
+        if (seen != (1 << pl->nchunks) - 1) {
+            set_last_error("tile plan: order[] is not a permutation of the chunk positions");
+            return -1;
+        }
+    }
     const bool multi = a.nsteps > 1;
     if (multi && (a.first || a.n < 2 || !a.epoch || !a.stepdone || a.desc)) {
         set_last_error("multi-layer launch needs n >= 2, epoch/stepdone arrays and no step descriptor");
@@ -1073,6 +1094,16 @@ int launch_step(const StepLaunch& a) {
     p.elo0 = b->elo[0]; p.ehi0 = b->ehi[0];
     p.nty = pl->nty; p.ntz = pl->ntz; p.nchunks = pl->nchunks; p.ty = pl->ty; p.tz = pl->tz;
     for (int c = 0; c <= pl->nchunks; c++) p.xcut[c] = pl->xcut[c];
+    for (int c = 0; c < pl->nchunks; c++) {
+        p.pos_of[c] = (signed char)pl->order[c];
+        p.pi_of[pl->order[c]] = (signed char)c;
+    }
+    p.self_wrap = b->nbr[0] == b->rank;
+    if (multi && p.self_wrap) {
+        // the wrap-around ghost planes are guarded by the per-item epochs of the end chunks, not by a
+        // whole-layer flag (which would turn every layer boundary back into a barrier)
+        p.flag_in[0] = p.flag_in[1] = nullptr;
+    }
     p.s1 = pl->s1; p.s0 = pl->s0;
     p.send_x0 = b->send_x[0]; p.send_x1 = b->send_x[1];
     {

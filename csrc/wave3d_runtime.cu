@@ -382,12 +382,13 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
             const double share = (double)ntiles * X / ctas;
             int minlen = std::max(4, std::min(X, std::max(8, X / 32)));
             if (const char* e = getenv("WAVE3D_MINLEN")) minlen = std::max(2, std::min(X, atoi(e)));
-            int cuts[18];
+            int cuts[18], ord[16];
             int m = 0;
             cuts[0] = 0;
             if (nov >= 3 && ov[2] > 0) {
                 m = std::min(16, std::min(ov[2], X));
                 for (int c = 1; c <= m; c++) cuts[c] = (int)((int64_t)X * c / m);
+                for (int i = 0; i < m; i++) ord[i] = (i % 2 == 0) ? i / 2 : m - 1 - i / 2;
             } else {
                 // built from the end of the column: two floor-sized chunks, then doubling up to the cap;
                 // what is left over goes to the front, where imbalance can still be repaired
@@ -403,9 +404,16 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
                 }
                 m = k;  // len[] is in back-to-front order
                 std::sort(len, len + m);
-                for (int c = 0; c < m; c++) cuts[c + 1] = cuts[c] + len[m - 1 - c];
+                std::reverse(len, len + m);  // len[i] = length of the i-th chunk in queue order (descending)
+                // zig-zag placement along x: queue order visits positions 0, m-1, 1, m-2, ...
+                int plen[16];
+                for (int i = 0; i < m; i++) {
+                    ord[i] = (i % 2 == 0) ? i / 2 : m - 1 - i / 2;
+                    plen[ord[i]] = len[i];
+                }
+                for (int c = 0; c < m; c++) cuts[c + 1] = cuts[c] + plen[c];
             }
-            const double tail = 0.5 * (cuts[m] - cuts[m - 1]) / std::max(1.0, share);
+            const double tail = 0.5 * (cuts[ord[m - 1] + 1] - cuts[ord[m - 1]]) / std::max(1.0, share);
             const double fill = std::max(1.0, (double)slots / ((double)ntiles * m));
             const double eff = (double)X / (X + m * r0) / (1.0 + tail) / fill /
                                (waste * (1.0 + 0.3 * halo) * rjf * occf * tlpf);
@@ -417,6 +425,7 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
                 plan->ctas = (int)std::min<int64_t>(ctas, (int64_t)ntiles * m);
                 plan->slots = slots; plan->efficiency = eff;
                 for (int c = 0; c <= m; c++) plan->xcut[c] = cuts[c];
+                for (int c = 0; c < m; c++) plan->order[c] = ord[c];
             }
         }
     }

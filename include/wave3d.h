@@ -189,7 +189,10 @@ typedef struct wave3d_plan {
     int32_t ctas;    /* persistent CTAs pulling (tile, x-chunk) items from a device-side queue, chunk-major */
     int32_t slots;   /* resident CTAs on the device */
     double efficiency; /* modelled useful fraction */
-    int32_t xcut[18];  /* chunk c covers owned planes [xcut[c], xcut[c+1]); sizes shrink towards the end */
+    int32_t xcut[18];  /* the chunk at position c along x covers owned planes [xcut[c], xcut[c+1]) */
+    int32_t order[16]; /* queue order within a layer: order[i] = position of the i-th chunk. Zig-zag from both
+                          ends (0, m-1, 1, m-2, ...) keeps x-adjacent chunks — the periodic wrap included —
+                          close in the queue; lengths shrink along this order */
 } wave3d_plan;
 
 /* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,nchunks[,s1,s0]" overrides (nchunks 0 = auto). */

@@ -23,6 +23,9 @@ def test_plan_is_feasible(N, nranks, dims):
         assert 1 <= pl.ctas <= pl.slots and pl.ctas <= pl.nty * pl.ntz * pl.nchunks
         assert 1 <= pl.nchunks <= 16 and pl.xcut[0] == 0 and pl.xcut[pl.nchunks] == box.n[0]
         assert all(pl.xcut[c] < pl.xcut[c + 1] for c in range(pl.nchunks))
+        assert sorted(pl.order[:pl.nchunks]) == list(range(pl.nchunks))
+        lens = [pl.xcut[pl.order[i] + 1] - pl.xcut[pl.order[i]] for i in range(pl.nchunks)]
+        assert lens == sorted(lens, reverse=True)  # guided: big chunks first in queue order
         assert (0.3 if N >= 256 else 0.0) < pl.efficiency <= 1.0
 
 
