@@ -43,7 +43,8 @@ struct StepLaunch {
     uint64_t* err;       // table base (2 words per layer)
     uint32_t* scratch;
     uint32_t* epoch;     // multi-layer launches: one word per (tile, chunk) item, zeroed before the solve
-    uint32_t* stepdone;  // multi-layer launches: one word per layer, zeroed before the solve
+    uint32_t* stepdone;  // multi-layer launches: 3*(timesteps+2) words (items per layer, then x-face items
+                         // per layer and side), zeroed before the solve
     const double* desc;  // device pointer to {arg_t, coef} or nullptr
     double spin_timeout_s;
     int div_mode;        // -1: choose

@@ -118,6 +118,7 @@ struct alignas(64) StepParams {
     uint32_t* scratch;
     uint32_t* epoch;     // multi-step mode: last completed layer per (tile, chunk) item
     uint32_t* stepdone;  // multi-step mode: completed items per layer
+    uint32_t* facedone;  // multi-step mode: completed x-face items per layer (2 words per layer)
     const double* desc;  // optional uploaded step descriptor {arg_t, coef} (single-step mode)
     int64_t ps, pitch;
     double coef, arg_t;
@@ -358,6 +359,19 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     const int n = p.n0 + gid / nitems, item = gid % nitems;
                     __threadfence();
                     st_release_gpu(p.epoch + item, (uint32_t)n);
+                    // The x faces are complete as soon as the two end chunks of every tile column are: they
+                    // come first in the queue, so the x neighbours get their flag almost a whole layer
+                    // before they need it (y/z faces span all chunks and are published with the layer).
+                    const int cpos = p.pos_of[item / ntiles];
+                    if (cpos == 0 && p.flag_out[0] && atomicAdd(p.facedone + 2 * n, 1u) == (uint32_t)ntiles - 1u) {
+                        __threadfence_system();
+                        st_release_sys(p.flag_out[0], (uint32_t)n + 1u);
+                    }
+                    if (cpos == p.nchunks - 1 && p.flag_out[1] &&
+                        atomicAdd(p.facedone + 2 * n + 1, 1u) == (uint32_t)ntiles - 1u) {
+                        __threadfence_system();
+                        st_release_sys(p.flag_out[1], (uint32_t)n + 1u);
+                    }
                     if (atomicAdd(p.stepdone + n, 1u) == (uint32_t)nitems - 1u) {
                         // layer n is complete on this rank
                         unsigned long long* e = reinterpret_cast<unsigned long long*>(p.err + 2 * (size_t)n);
@@ -368,7 +382,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                             atomicMax_system(re, va);
                             atomicMax_system(re + 1, vr);
                         }
-                        for (int f = 0; f < 6; f++)
+                        for (int f = 2; f < 6; f++)
                             if (p.flag_out[f]) st_release_sys(p.flag_out[f], (uint32_t)n + 1u);
                     }
                     pub_kq++;
@@ -1073,6 +1087,7 @@ int launch_step(const StepLaunch& a) {
     p.root_err = pw.root_err;
     p.epoch = a.epoch;
     p.stepdone = a.stepdone;
+    p.facedone = a.stepdone ? a.stepdone + (pr->timesteps + 2) : nullptr;
     p.n0 = a.n;
     p.nsteps = multi ? a.nsteps : 1;
     p.a_t = pr->a_t;

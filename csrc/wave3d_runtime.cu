@@ -122,7 +122,7 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     r.epoch_bytes = align_up((size_t)r.plan.nty * r.plan.ntz * r.plan.nchunks * 4, 256);
     off += r.epoch_bytes;
     r.off_stepdone = off;
-    r.stepdone_bytes = align_up((size_t)(s->prob.timesteps + 2) * 4, 256);
+    r.stepdone_bytes = align_up((size_t)(s->prob.timesteps + 2) * 4 * 3, 256);
     off += r.stepdone_bytes;
     r.slab_bytes = off;
     W3D_TRY(cudaMalloc(&r.slab, r.slab_bytes));
