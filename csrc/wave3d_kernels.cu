@@ -326,8 +326,9 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             // Neighbours must have finished the previous layer: their ghost stores are complete (RAW)
             // and they no longer read the ghosts this layer overwrites (WAR). Nothing of this CTA
             // touches global memory before its first plane has arrived, i.e. after this wait.
-            const unsigned long long t0 = globaltimer_ns();
+            // every wait is bounded on its own (a dead peer must not hang the GPU, a long solve must not trip it)
             auto wait_flag = [&](const uint32_t* fl, uint32_t need, bool sys) {
+                const unsigned long long t0 = globaltimer_ns();
                 while ((sys ? ld_acquire_sys(fl) : ld_acquire_gpu(fl)) < need) {
                     __nanosleep(32);
                     if (globaltimer_ns() - t0 > p.timeout_ns) {
@@ -445,6 +446,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     if (tzi == 0 && p.flag_in[4]) { wp[nw] = p.flag_in[4]; wn[nw++] = needf; }
                     if (tzi == p.ntz - 1 && p.flag_in[5]) { wp[nw] = p.flag_in[5]; wn[nw++] = needf; }
                     if (nw) {
+                        const unsigned long long t0 = globaltimer_ns();
                         for (;;) {
                             bool ok = true;
                             for (int q = 0; q < nw; q++)

@@ -295,12 +295,12 @@ int enqueue_step_rank(wave3d_solver* s, Rank& r, int n, const double* pinned_des
 }
 
 // Layers n0 .. timesteps of one rank in a single persistent cooperative launch (k_step<..., MULTI>).
-int enqueue_multi_rank(wave3d_solver* s, Rank& r, int n0) {
+int enqueue_multi_rank(wave3d_solver* s, Rank& r, int n0, int nsteps) {
     if (use_device(r.device)) return -1;
     StepLaunch a;
     fill_launch(s, r, a);
     a.n = n0;
-    a.nsteps = s->prob.timesteps - n0 + 1;
+    a.nsteps = nsteps;
     a.first = 0;
     if (launch_step(a)) return -1;
     s->launches++;
@@ -968,7 +968,15 @@ static int enqueue_all(wave3d_solver* s, Group* only) {
     const bool multi = multistep_ok(s);
     for (int n = 1; n <= s->prob.timesteps; n++) {
         if (multi && n == 2) {
-            if (members([&](Rank& r) { return enqueue_multi_rank(s, r, 2); })) return -1;
+            // one launch per 2048 layers keeps the item counter far from 2^31 on very long runs
+            for (int n0 = 2; n0 <= s->prob.timesteps; n0 += 2048) {
+                const int ns = std::min(2048, s->prob.timesteps - n0 + 1);
+                if (ns == 1) {
+                    if (members([&](Rank& r) { return enqueue_step_rank(s, r, n0, nullptr); })) return -1;
+                } else if (members([&](Rank& r) { return enqueue_multi_rank(s, r, n0, ns); })) {
+                    return -1;
+                }
+            }
             break;
         }
         if (members([&](Rank& r) { return enqueue_step_rank(s, r, n, nullptr); })) return -1;
