@@ -710,9 +710,16 @@ int wave3d_solver_enqueue_step(wave3d_solver* s, int n) {
             if (enqueue_step_rank(s, r, n, nullptr)) return -1;
         return 0;
     }
-    for (auto& r : s->ranks) {
+    // Ranks are independent within a layer. With one thread per rank (the pure "MPI" flavour of the
+    // reference) the local ranks run side by side; with several threads per rank (OpenMP / hybrid
+    // flavour) each rank's loop nest is threaded instead.
+    const int nl = (int)s->ranks.size();
+    const bool side_by_side = nl > 1 && s->opts.threads <= 1;
+#pragma omp parallel for schedule(static) if (side_by_side)
+    for (int l = 0; l < nl; l++) {
+        Rank& r = s->ranks[l];
         wave3d_cpu_step(&s->prob, &r.box, &r.lay, r.hfield[(n & 1) ^ 1].data(), r.hfield[n & 1].data(), n, n == 1,
-                        &r.habs[n], &r.hrel[n], s->opts.threads);
+                        &r.habs[n], &r.hrel[n], side_by_side ? 1 : s->opts.threads);
         if (n == 1) wave3d_cpu_zero_walls(&r.box, &r.lay, r.hfield[0].data());
     }
     return 0;
