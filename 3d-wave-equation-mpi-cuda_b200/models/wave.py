@@ -185,6 +185,11 @@ class WaveSolver:
     def status(self) -> int:
         return _lib.lib().wave3d_solver_status(self._h)
 
+    @property
+    def multistep_active(self) -> bool:
+        """True when layers 2..T run in the persistent multi-layer launch (small boxes, one rank per GPU)."""
+        return bool(_lib.lib().wave3d_solver_multistep_active(self._h))
+
     def export(self, local: int = 0) -> _lib.Export:
         e = _lib.Export()
         self._chk(_lib.lib().wave3d_solver_export(self._h, local, C.byref(e)), "solver_export")
@@ -235,7 +240,9 @@ class WaveSolver:
         self._chk(rc, "solver_run_streamed")
         return SolveResult([out[2 * n] for n in range(L)], [out[2 * n + 1] for n in range(L)], t.solve_ms, self.init_ms,
                            self.launches - before, self.nranks, self.dims, self.problem.cells, self.problem.timesteps,
-                           {"h2d_bytes_per_step": 16 * self.nlocal, "d2h_bytes_per_step": 16 * self.nlocal, "lag": lag})
+                           {"h2d_bytes_per_step": 16 * self.nlocal,
+                            "d2h_bytes_per_step": (20 if self.multistep_active else 16) * self.nlocal,
+                            "lag": lag, "multi_layer_launch": self.multistep_active})
 
     def run_per_step(self, progress=None) -> SolveResult:
         """Reference-style driver: after every layer the maxima are read back to the host

@@ -133,13 +133,19 @@ def run_ours(a):
         t_e2e, r_e2e = streamed(1)
         t_sync, _ = streamed(0)
         assert r_e2e.max_abs[-1] == res.max_abs[-1] or distributed  # same solve (local maxima under torchrun)
-        e2e = {"value": cells * K / (t_e2e * 1e-3) / 1e9, "unit": "Gcell-updates/s", "h2d_bytes_per_step": 16,
-               "d2h_bytes_per_step": 16, "ms_per_step": t_e2e / K, "lag_layers": 1,
+        ml = bool(r_e2e.extra.get("multi_layer_launch"))
+        e2e = {"value": cells * K / (t_e2e * 1e-3) / 1e9, "unit": "Gcell-updates/s",
+               "h2d_bytes_per_step": r_e2e.extra["h2d_bytes_per_step"], "d2h_bytes_per_step": r_e2e.extra["d2h_bytes_per_step"],
+               "ms_per_step": t_e2e / K, "lag_layers": 1, "multi_layer_launch": ml,
                "sync_value": cells * K / (t_sync * 1e-3) / 1e9,
-               "note": "WaveSolver.run_streamed: every layer copies its step descriptor pinned->device, runs the fused "
-                       "kernel and copies its max abs/rel error device->host; the host reads layer n while layer n+1 "
-                       "runs (sync_value: host waits for every layer before launching the next). Wall clock incl. "
-                       "layer 0, max over ranks; bytes are per rank"}
+               "note": ("WaveSolver.run_streamed, small-box path: layers 2..T run in the persistent multi-layer launch; every "
+                        "layer's step descriptor is copied pinned->device on a copy stream while the kernel runs (the "
+                        "kernel waits for it), every layer's max abs/rel error is written to mapped pinned host memory "
+                        "with a ready flag that the host polls. " if ml else
+                        "WaveSolver.run_streamed: every layer copies its step descriptor pinned->device, runs the fused "
+                        "kernel and copies its max abs/rel error device->host; the host reads layer n while layer n+1 "
+                        "runs (sync_value: host waits for every layer before launching the next). ") +
+                       "Wall clock incl. layer 0, max over ranks; bytes are per rank"}
     # roofline: 24 B of HBM traffic per cell per step (read u^{n-1}, read u^{n-2}, write u^n) against the
     # MEASURED copy bandwidth of this pool (MEASURED_PEAKS.json; fallback 6650 GB/s, B200_PROFILING.md)
     hbm, src = 6650.0, "fallback"

@@ -46,6 +46,11 @@ struct StepLaunch {
     uint32_t* stepdone;  // multi-layer launches: 3*(timesteps+2) words (items per layer, then x-face items
                          // per layer and side), zeroed before the solve
     const double* desc;  // device pointer to {arg_t, coef} or nullptr
+    // streamed multi-layer launch: descriptor table in device memory (NaN until uploaded), mapped host
+    // memory for the layer maxima and their ready flags
+    const double* desc_tab;
+    double* host_res;
+    uint32_t* host_flag;
     double spin_timeout_s;
     int div_mode;        // -1: choose
     cudaStream_t stream;

@@ -120,6 +120,9 @@ struct alignas(64) StepParams {
     uint32_t* stepdone;  // multi-step mode: completed items per layer
     uint32_t* facedone;  // multi-step mode: completed x-face items per layer (2 words per layer)
     const double* desc;  // optional uploaded step descriptor {arg_t, coef} (single-step mode)
+    const double* desc_tab;   // multi-step streamed mode: descriptor table [layer][2] in device memory, NaN until uploaded
+    double* host_res;         // multi-step streamed mode: mapped host memory, layer maxima [layer][2]
+    uint32_t* host_flag;      // multi-step streamed mode: mapped host memory, 1 when host_res[layer] is valid
     int64_t ps, pitch;
     double coef, arg_t;
     double a_t, tau, twopi;  // multi-step mode: cos(fma(a_t*n, tau, twopi)) per layer
@@ -385,6 +388,14 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                         }
                         for (int f = 2; f < 6; f++)
                             if (p.flag_out[f]) st_release_sys(p.flag_out[f], (uint32_t)n + 1u);
+                        if (p.host_res) {
+                            // streamed mode: the layer's result goes straight to the host (mapped pinned memory)
+                            const unsigned long long va = atomicMax(e, 0ull), vr = atomicMax(e + 1, 0ull);
+                            reinterpret_cast<volatile unsigned long long*>(p.host_res)[2 * (size_t)n] = va;
+                            reinterpret_cast<volatile unsigned long long*>(p.host_res)[2 * (size_t)n + 1] = vr;
+                            __threadfence_system();
+                            st_release_sys(p.host_flag + n, 1u);
+                        }
                     }
                     pub_kq++;
                 }
@@ -491,7 +502,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
     } else {
         // ================================ compute warps ================================
         double cosn = s_bcast[0], rcos = s_bcast[1];
-        const double coef = s_bcast[2];
+        double coef = s_bcast[2];
         const double hx2 = p.hx2, hy2 = p.hy2, hz2 = p.hz2, rx = p.rx, ry = p.ry, rz = p.rz;
         const int64_t ps = p.ps;
         const bool xpush = (p.push_mask & 3u) != 0;
@@ -522,7 +533,25 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                 // a new layer: its cosine, and fresh maxima (within a layer the running maxima and the
                 // rel-error filter threshold carry over from item to item; re-publishing a maximum is harmless)
                 cur_n = n;
-                cosn = cos(__fma_rn(__dmul_rn(p.a_t, (double)n), p.tau, p.twopi));
+                double arg_t = __fma_rn(__dmul_rn(p.a_t, (double)n), p.tau, p.twopi);
+                if (p.desc_tab) {
+                    // streamed (end-to-end) mode: this layer's inputs are being copied host->device while
+                    // the kernel runs; the table holds NaN until the copy of layer n has landed
+                    const volatile double* d = p.desc_tab + 2 * (size_t)n;
+                    double a0 = d[0], a1 = d[1];
+                    if (lane == 0) {
+                        const unsigned long long t0 = globaltimer_ns();
+                        while ((a0 != a0 || a1 != a1) && globaltimer_ns() - t0 < p.timeout_ns) {
+                            __nanosleep(64);
+                            a0 = d[0];
+                            a1 = d[1];
+                        }
+                        if (a0 != a0 || a1 != a1) atomicExch(&p.scratch[1], 1u);
+                    }
+                    arg_t = __shfl_sync(0xffffffffu, a0, 0);
+                    coef = __shfl_sync(0xffffffffu, a1, 0);
+                }
+                cosn = cos(arg_t);
                 rcos = __ddiv_rn(1.0, fabs(cosn));
                 ea.mabs = ea.mrel = ea.best = ea.thr = 0.0;
             }
@@ -1063,6 +1092,10 @@ int launch_step(const StepLaunch& a) {
         }
     }
     const bool multi = a.nsteps > 1;
+    if (a.nsteps == 1 && a.desc_tab) {
+        set_last_error("the streamed descriptor table needs a multi-layer launch");
+        return -1;
+    }
     if (multi && (a.first || a.n < 2 || !a.epoch || !a.stepdone || a.desc)) {
         set_last_error("multi-layer launch needs n >= 2, epoch/stepdone arrays and no step descriptor");
         return -1;
@@ -1090,6 +1123,9 @@ int launch_step(const StepLaunch& a) {
     p.epoch = a.epoch;
     p.stepdone = a.stepdone;
     p.facedone = a.stepdone ? a.stepdone + (pr->timesteps + 2) : nullptr;
+    p.desc_tab = multi ? a.desc_tab : nullptr;
+    p.host_res = multi ? a.host_res : nullptr;
+    p.host_flag = multi ? a.host_flag : nullptr;
     p.n0 = a.n;
     p.nsteps = multi ? a.nsteps : 1;
     p.a_t = pr->a_t;

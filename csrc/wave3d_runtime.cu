@@ -41,6 +41,9 @@ struct Rank {
     size_t epoch_bytes = 0, stepdone_bytes = 0;
     uint32_t* epoch = nullptr;     // multi-layer launch: last completed layer per (tile, chunk) item
     uint32_t* stepdone = nullptr;  // multi-layer launch: completed items per layer
+    unsigned char* hmap = nullptr; // streamed multi-layer launch: mapped pinned memory (layer maxima + flags)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy = nullptr;
     double* field[2] = {nullptr, nullptr};
     double* tabs[6] = {nullptr};
     uint64_t* err = nullptr;
@@ -295,16 +298,29 @@ int enqueue_step_rank(wave3d_solver* s, Rank& r, int n, const double* pinned_des
 }
 
 // Layers n0 .. timesteps of one rank in a single persistent cooperative launch (k_step<..., MULTI>).
-int enqueue_multi_rank(wave3d_solver* s, Rank& r, int n0, int nsteps) {
+int enqueue_multi_rank(wave3d_solver* s, Rank& r, int n0, int nsteps, bool streamed = false) {
     if (use_device(r.device)) return -1;
     StepLaunch a;
     fill_launch(s, r, a);
     a.n = n0;
     a.nsteps = nsteps;
     a.first = 0;
+    if (streamed) {
+        a.desc_tab = r.desc;
+        a.host_res = reinterpret_cast<double*>(r.hmap);
+        a.host_flag = reinterpret_cast<uint32_t*>(r.hmap + (size_t)(s->prob.timesteps + 2) * 16);
+    }
     if (launch_step(a)) return -1;
     s->launches++;
     return 0;
+}
+
+// Layers per multi-layer launch: at most 2048 (keeps the item counter far from 2^31 on very long runs) and
+// never a left-over single layer (which would need the per-layer kernel).
+int multi_chunk(int T) {
+    int size = 2048;
+    while (T - 1 > size && (T - 1) % size == 1) size--;
+    return size;
 }
 
 // The multi-layer launch keeps a rank's kernel resident across layers while it waits for its
@@ -468,6 +484,9 @@ void wave3d_solver_destroy(wave3d_solver* s) {
             }
             if (r.ev_packed) cudaEventDestroy(r.ev_packed);
             if (r.ev_unpacked) cudaEventDestroy(r.ev_unpacked);
+            if (r.hmap) cudaFreeHost(r.hmap);
+            if (r.copy_stream) cudaStreamDestroy(r.copy_stream);
+            if (r.ev_copy) cudaEventDestroy(r.ev_copy);
             if (r.slab) cudaFree(r.slab);
         }
         for (cudaEvent_t e : s->xev) cudaEventDestroy(e);
@@ -881,6 +900,89 @@ int wave3d_solver_run_streamed(wave3d_solver* s, const double* pinned_desc, int 
         s->sev.push_back(e);
     }
     for (int i = 0; i < 2 * (T + 1); i++) abs_rel[i] = 0.0;
+    if (!staged && multistep_ok(s)) {
+        // ---- small boxes: layers 2..T run in the persistent multi-layer launch while the host streams the
+        // per-layer inputs in (one pinned->device copy per layer on a copy stream; the kernel waits for
+        // layer n's descriptor to land) and the kernel streams the per-layer results out (maxima + ready
+        // flag written to mapped pinned memory when a layer completes; the host polls the flag).
+        const size_t res_bytes = (size_t)(T + 2) * 16, map_bytes = res_bytes + (size_t)(T + 2) * 4;
+        for (auto& r : s->ranks) {
+            if (use_device(r.device)) return -1;
+            if (!r.hmap) {
+                W3D_TRY(cudaHostAlloc(&r.hmap, map_bytes, cudaHostAllocMapped | cudaHostAllocPortable));
+                W3D_TRY(cudaStreamCreateWithFlags(&r.copy_stream, cudaStreamNonBlocking));
+                W3D_TRY(cudaEventCreateWithFlags(&r.ev_copy, cudaEventDisableTiming));
+            }
+            memset(r.hmap, 0, map_bytes);
+        }
+        auto t0 = std::chrono::steady_clock::now();
+        for (auto& r : s->ranks) {
+            if (use_device(r.device)) return -1;
+            cudaStream_t st = stream_of(s, r);
+            W3D_TRY(cudaMemsetAsync(r.desc, 0xFF, (size_t)(T + 1) * 16, st));  // all-ones = NaN: "not uploaded yet"
+            W3D_TRY(cudaEventRecord(r.ev_copy, st));
+            W3D_TRY(cudaStreamWaitEvent(r.copy_stream, r.ev_copy, 0));
+            if (enqueue_layer0_rank(s, r)) return -1;
+            if (enqueue_step_rank(s, r, 1, pinned_desc + 2)) return -1;
+            W3D_TRY(cudaMemcpyAsync(s->pinned + 2 * ((size_t)1 * L + r.local), r.err + 2, 16, cudaMemcpyDeviceToHost, st));
+        }
+        for (size_t g = 0; g < s->groups.size(); g++) {
+            if (use_device(s->groups[g].device)) return -1;
+            W3D_TRY(cudaEventRecord(s->sev[s->groups.size() + g], s->groups[g].stream));
+        }
+        const int chunk = multi_chunk(T);
+        for (int n0 = 2; n0 <= T; n0 += chunk) {
+            const int ns = std::min(chunk, T - n0 + 1);
+            for (auto& r : s->ranks)
+                if (enqueue_multi_rank(s, r, n0, ns, true)) return -1;
+        }
+        for (int n = 2; n <= T; n++)
+            for (auto& r : s->ranks) {
+                if (use_device(r.device)) return -1;
+                W3D_TRY(cudaMemcpyAsync(r.desc + 2 * n, pinned_desc + 2 * n, 16, cudaMemcpyHostToDevice, r.copy_stream));
+            }
+        // layer 1 came through the per-layer path
+        for (size_t g = 0; g < s->groups.size(); g++) {
+            if (use_device(s->groups[g].device)) return -1;
+            W3D_TRY(cudaEventSynchronize(s->sev[s->groups.size() + g]));
+        }
+        for (auto& r : s->ranks) {
+            const double* src = s->pinned + 2 * ((size_t)1 * L + r.local);
+            r.habs[1] = src[0];
+            r.hrel[1] = src[1];
+            abs_rel[2] = std::max(abs_rel[2], src[0]);
+            abs_rel[3] = std::max(abs_rel[3], src[1]);
+        }
+        const auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(120);
+        for (int n = 2; n <= T; n++) {
+            for (auto& r : s->ranks) {
+                volatile uint32_t* flag = reinterpret_cast<volatile uint32_t*>(r.hmap + res_bytes) + n;
+                while (*flag == 0) {
+                    if (std::chrono::steady_clock::now() > deadline) {
+                        set_last_error("streamed solve: layer result did not arrive");
+                        return -2;
+                    }
+                }
+                __sync_synchronize();
+                const double* src = reinterpret_cast<const double*>(r.hmap) + 2 * (size_t)n;
+                r.habs[n] = src[0];
+                r.hrel[n] = src[1];
+                abs_rel[2 * n] = std::max(abs_rel[2 * n], src[0]);
+                abs_rel[2 * n + 1] = std::max(abs_rel[2 * n + 1], src[1]);
+            }
+        }
+        if (wave3d_solver_sync(s)) return -1;
+        for (auto& r : s->ranks) {
+            if (use_device(r.device)) return -1;
+            W3D_TRY(cudaStreamSynchronize(r.copy_stream));
+        }
+        auto t1 = std::chrono::steady_clock::now();
+        if (t) {
+            memset(t, 0, sizeof *t);
+            t->solve_ms = t->loop_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        }
+        return wave3d_solver_status(s) ? -2 : 0;
+    }
     auto collect = [&](int n) -> int {
         for (size_t g = 0; g < s->groups.size(); g++) {
             if (use_device(s->groups[g].device)) return -1;
@@ -926,6 +1028,8 @@ int wave3d_solver_run_streamed(wave3d_solver* s, const double* pinned_desc, int 
 }
 
 int64_t wave3d_solver_kernel_launches(const wave3d_solver* s) { return s ? s->launches : 0; }
+
+int wave3d_solver_multistep_active(const wave3d_solver* s) { return s && multistep_ok(s) ? 1 : 0; }
 
 int wave3d_solver_status(wave3d_solver* s) {
     if (!s || s->opts.backend != WAVE3D_BACKEND_CUDA) return 0;
@@ -976,13 +1080,10 @@ static int enqueue_all(wave3d_solver* s, Group* only) {
     for (int n = 1; n <= s->prob.timesteps; n++) {
         if (multi && n == 2) {
             // one launch per 2048 layers keeps the item counter far from 2^31 on very long runs
-            for (int n0 = 2; n0 <= s->prob.timesteps; n0 += 2048) {
-                const int ns = std::min(2048, s->prob.timesteps - n0 + 1);
-                if (ns == 1) {
-                    if (members([&](Rank& r) { return enqueue_step_rank(s, r, n0, nullptr); })) return -1;
-                } else if (members([&](Rank& r) { return enqueue_multi_rank(s, r, n0, ns); })) {
-                    return -1;
-                }
+            const int chunk = multi_chunk(s->prob.timesteps);
+            for (int n0 = 2; n0 <= s->prob.timesteps; n0 += chunk) {
+                const int ns = std::min(chunk, s->prob.timesteps - n0 + 1);
+                if (members([&](Rank& r) { return enqueue_multi_rank(s, r, n0, ns); })) return -1;
             }
             break;
         }

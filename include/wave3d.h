@@ -366,6 +366,8 @@ int wave3d_solver_errors(wave3d_solver* s, double* max_abs, double* max_rel);
 /* Error maxima of one layer, read back synchronously (per-step mode). */
 int wave3d_solver_layer_error(wave3d_solver* s, int n, double* abs_rel2);
 int64_t wave3d_solver_kernel_launches(const wave3d_solver* s);
+/* 1 if run()/run_streamed() use the persistent multi-layer launch for layers 2..T (small boxes, one rank per GPU). */
+int wave3d_solver_multistep_active(const wave3d_solver* s);
 int wave3d_solver_status(wave3d_solver* s); /* 0 ok; 1 in-kernel spin timeout on some rank */
 
 /* The reference program end to end: parse, print "C = ...", solve, write the report. */

@@ -174,3 +174,18 @@ def test_streamed_solve_equals_batch_solve(lag):
         got = s.run_streamed(lag=lag)
     assert got.max_abs == ref.max_abs and got.max_rel == ref.max_rel
     assert got.extra["h2d_bytes_per_step"] == 32 and got.solve_ms > 0
+
+
+def test_streamed_solve_over_the_multi_layer_launch(monkeypatch):
+    """Single rank, small box: run_streamed keeps the persistent multi-layer launch; descriptors stream in
+    on a copy stream (the kernel waits for each layer's to land), maxima stream out through mapped memory."""
+    monkeypatch.setenv("WAVE3D_MULTISTEP", "1")
+    p = w.Problem(N=72, Lx=1.0, Ly=2.0, Lz=_lib.PI_FULL, T=0.05, timesteps=11)
+    with w.WaveSolver(p, backend="cuda") as s:
+        ref = s.run()
+        a = s.run_streamed()
+        b = s.run_streamed()
+        assert s.status() == 0
+        assert a.launches < p.timesteps  # one launch for layers 2..T
+    assert a.max_abs == ref.max_abs and a.max_rel == ref.max_rel
+    assert b.max_abs == ref.max_abs and b.max_rel == ref.max_rel
