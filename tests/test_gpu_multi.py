@@ -38,3 +38,4 @@ def test_one_rank_per_gpu(tmp_path, nproc, dims, transport):
     assert got["abs2"] == ref.max_abs and got["rel2"] == ref.max_rel
     if transport == "peer":
         assert got["extra"].get("root_table_matches_allreduce") is True
+        assert got["streamed_ok"] is True
