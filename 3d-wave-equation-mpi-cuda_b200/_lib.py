@@ -160,6 +160,7 @@ def _sig(lib):
         "wave3d_solver_errors": (i32, [vp, D, D]),
         "wave3d_solver_layer_error": (i32, [vp, i32, D]),
         "wave3d_solver_kernel_launches": (i64, [vp]),
+        "wave3d_solver_field_error": (i32, [vp, i32, D]),
         "wave3d_solver_status": (i32, [vp]),
         "wave3d_solver_multistep_active": (i32, [vp]),
         "wave3d_main": (i32, [i32, C.POINTER(cs)]),

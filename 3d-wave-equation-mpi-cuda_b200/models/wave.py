@@ -171,6 +171,13 @@ class WaveSolver:
         self._chk(_lib.lib().wave3d_solver_layer_error(self._h, n, e), "layer_error")
         return e[0], e[1]
 
+    def field_error(self, n: int):
+        """(max abs, max rel) of the *stored* layer n against the analytic solution, as a separate post-pass
+        (ref: calculate_error(), mpi_sol.cpp:340-372). After a solve the last two layers are resident."""
+        e = (C.c_double * 2)()
+        self._chk(_lib.lib().wave3d_solver_field_error(self._h, n, e), "solver_field_error")
+        return e[0], e[1]
+
     def errors(self):
         L = self.problem.timesteps + 1
         a = (C.c_double * L)()

@@ -41,6 +41,7 @@ struct Rank {
     size_t epoch_bytes = 0, stepdone_bytes = 0;
     uint32_t* epoch = nullptr;     // multi-layer launch: last completed layer per (tile, chunk) item
     uint32_t* stepdone = nullptr;  // multi-layer launch: completed items per layer
+    uint64_t* ferr_scratch = nullptr;  // scratch of the stand-alone error evaluation (zeroed with the slab)
     unsigned char* hmap = nullptr; // streamed multi-layer launch: mapped pinned memory (layer maxima + flags)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copy = nullptr;
@@ -138,6 +139,7 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     r.scratch = reinterpret_cast<uint32_t*>(r.slab + r.off_scratch);
     r.desc = reinterpret_cast<double*>(r.slab + r.off_desc);
     r.epoch = reinterpret_cast<uint32_t*>(r.slab + r.off_epoch);
+    r.ferr_scratch = reinterpret_cast<uint64_t*>(r.slab + r.off_ferr);
     r.stepdone = reinterpret_cast<uint32_t*>(r.slab + r.off_stepdone);
     for (int w = 0; w < 2; w++) {
         if (encode_field_map(&r.map_halo[w], r.field[w], &r.lay, r.plan.tz + 4, r.plan.ty + 2)) return -1;
@@ -1025,6 +1027,39 @@ int wave3d_solver_run_streamed(wave3d_solver* s, const double* pinned_desc, int 
         t->solve_ms = t->loop_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
     }
     return wave3d_solver_status(s) ? -2 : 0;
+}
+
+// Post-pass error of the stored layer n (it must still be resident: n or n-1 of the last computed layer),
+// the shape of the reference's first-generation calculate_error() (ref: mpi_sol.cpp:340-372): evaluated
+// by the stand-alone two-stage reduction, maximum over the local ranks.
+int wave3d_solver_field_error(wave3d_solver* s, int n, double* abs_rel2) {
+    if (!s || n < 0 || n > s->prob.timesteps || !abs_rel2) return -1;
+    abs_rel2[0] = abs_rel2[1] = 0.0;
+    if (s->opts.backend != WAVE3D_BACKEND_CUDA) {
+        for (auto& r : s->ranks) {
+            double a = 0.0, b = 0.0;
+            wave3d_cpu_field_error(&s->prob, &r.box, &r.lay, r.hfield[n & 1].data(), n, &a, &b, s->opts.threads);
+            abs_rel2[0] = std::max(abs_rel2[0], a);
+            abs_rel2[1] = std::max(abs_rel2[1], b);
+        }
+        return 0;
+    }
+    if (wave3d_solver_sync(s)) return -1;
+    for (auto& r : s->ranks) {
+        if (use_device(r.device)) return -1;
+        cudaStream_t st = stream_of(s, r);
+        double* out = r.desc;  // two doubles of device scratch; the descriptor table is idle between solves
+        const double* tabs[6] = {r.tabs[0], r.tabs[1], r.tabs[2], r.tabs[3], r.tabs[4], r.tabs[5]};
+        if (wave3d_cuda_field_error(&s->prob, &r.box, &r.lay, tabs, r.field[n & 1], n, r.ferr_scratch, out, st)) return -1;
+        s->launches++;
+        W3D_TRY(cudaMemcpyAsync(s->pinned + 2 * r.local, out, 16, cudaMemcpyDeviceToHost, st));
+    }
+    if (wave3d_solver_sync(s)) return -1;
+    for (auto& r : s->ranks) {
+        abs_rel2[0] = std::max(abs_rel2[0], s->pinned[2 * r.local]);
+        abs_rel2[1] = std::max(abs_rel2[1], s->pinned[2 * r.local + 1]);
+    }
+    return 0;
 }
 
 int64_t wave3d_solver_kernel_launches(const wave3d_solver* s) { return s ? s->launches : 0; }

@@ -365,6 +365,9 @@ int wave3d_solver_run_streamed(wave3d_solver* s, const double* pinned_desc, int 
 int wave3d_solver_errors(wave3d_solver* s, double* max_abs, double* max_rel);
 /* Error maxima of one layer, read back synchronously (per-step mode). */
 int wave3d_solver_layer_error(wave3d_solver* s, int n, double* abs_rel2);
+/* Post-pass error of the stored layer n (n = timesteps or timesteps-1 after a solve), evaluated by the
+ * stand-alone reduction — the shape of the first-generation reference programs' calculate_error(). */
+int wave3d_solver_field_error(wave3d_solver* s, int n, double* abs_rel2);
 int64_t wave3d_solver_kernel_launches(const wave3d_solver* s);
 /* 1 if run()/run_streamed() use the persistent multi-layer launch for layers 2..T (small boxes, one rank per GPU). */
 int wave3d_solver_multistep_active(const wave3d_solver* s);

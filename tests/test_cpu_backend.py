@@ -178,3 +178,11 @@ def test_per_step_driver_matches_run():
         a = s.run()
         b = s.run_per_step()
     assert a.max_abs == b.max_abs and a.max_rel == b.max_rel
+
+
+def test_post_pass_field_error_equals_fused_error():
+    p = w.Problem(N=22, Lx=1.0, Ly=2.0, Lz=3.0, T=0.05, timesteps=6)
+    with w.WaveSolver(p, nranks=4, backend="cpu") as s:
+        res = s.run()
+        assert s.field_error(6) == (res.max_abs[6], res.max_rel[6])
+        assert s.field_error(5) == (res.max_abs[5], res.max_rel[5])

@@ -189,3 +189,13 @@ def test_streamed_solve_over_the_multi_layer_launch(monkeypatch):
         assert a.launches < p.timesteps  # one launch for layers 2..T
     assert a.max_abs == ref.max_abs and a.max_rel == ref.max_rel
     assert b.max_abs == ref.max_abs and b.max_rel == ref.max_rel
+
+
+def test_post_pass_field_error_equals_fused_error():
+    p = w.Problem(N=50, Lx=1.0, Ly=2.0, Lz=3.0, T=0.05, timesteps=6)
+    for nranks in (1, 4):
+        with w.WaveSolver(p, nranks=nranks, backend="cuda", devices=[0]) as s:
+            res = s.run()
+            assert s.field_error(6) == (res.max_abs[6], res.max_rel[6])
+            assert s.field_error(5) == (res.max_abs[5], res.max_rel[5])
+            assert s.run().max_abs == res.max_abs  # the scratch borrowed for the post-pass does not disturb a solve
