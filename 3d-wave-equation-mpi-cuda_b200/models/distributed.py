@@ -113,6 +113,24 @@ class DistributedWaveSolver:
 
     solve = run
 
+    def make_descriptors(self):
+        return self.inner.make_descriptors()
+
+    def run_streamed(self, desc=None, lag: int = 1) -> SolveResult:
+        """End-to-end solve (peer transport): like :meth:`WaveSolver.run_streamed` on every rank — each layer's
+        inputs are copied from pinned host memory and its maxima are read back while the solve runs — with the
+        per-layer maxima and the wall time reduced with MAX over the ranks."""
+        if self.transport != "peer":
+            raise RuntimeError("run_streamed needs the peer transport (the staged path is driven step by step)")
+        p = self.problem
+        self._reset()
+        r = self.inner.run_streamed(desc, lag=lag)
+        self._barrier()
+        L = p.timesteps + 1
+        red = pdist.max_over_ranks(list(r.max_abs) + list(r.max_rel) + [r.solve_ms], self.coll_device)
+        return SolveResult(red[:L], red[L:2 * L], red[2 * L], 0.0, r.launches, self.world, self.dims, p.cells,
+                           p.timesteps, dict(r.extra, local_ms=r.solve_ms))
+
     def _run_staged(self) -> float:
         p, s = self.problem, self.inner
         if self.backend == "cuda":

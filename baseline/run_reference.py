@@ -81,7 +81,35 @@ def run_all_ranks_local(prog: str, argv, nranks: int, cwd: str, binary: str | No
     return outs
 
 
-def bench(a, tau: float):
+def dims_create(nranks: int):
+    """Process grid the reference gets from MPI_Dims_create (ref: cuda_sol.cpp:478): balanced, non-increasing.
+    Plain Python on purpose — this arm loads nothing of the repo's native code."""
+    primes, m, f = [], nranks, 2
+    while f * f <= m:
+        while m % f == 0:
+            primes.append(f)
+            m //= f
+        f += 1
+    if m > 1:
+        primes.append(m)
+    d = [1, 1, 1]
+    for f in sorted(primes, reverse=True):
+        d[d.index(min(d))] *= f
+    return tuple(sorted(d, reverse=True))
+
+
+def staged_bytes_per_step(N: int, dims):
+    """Bytes the reference moves between host and device inside its timed region, per step and per rank
+    (rank 0's block): exchange() copies all six padded send faces device->host and all six receive faces
+    host->device whether or not a neighbour exists (ref: cuda_sol.cpp:236-243, 296-304); calculate_errors
+    copies two arrays of one double per 512-cell block device->host (ref: cuda_sol_kernels.cu:80-88)."""
+    X, Y, Z = ((N + 1) // d for d in dims)
+    faces = 2 * ((Y + 2) * (Z + 2) + (X + 2) * (Z + 2) + (X + 2) * (Y + 2)) * 8
+    blocks = -(-((X + 2) * (Y + 2) * (Z + 2)) // 512)
+    return faces, faces + 2 * blocks * 8
+
+
+def bench(a, tau: float, problem_config):
     """bench.py --impl reference: same metric/config as our arm, one JSON line from rank 0."""
     rank = int(os.environ.get("RANK", "0"))
     ws = int(os.environ.get("WORLD_SIZE", "1"))
@@ -114,7 +142,22 @@ def bench(a, tau: float):
     argv = [N, 1, L, L, L, repr(T), K]
     face = (N + 3) * (N + 3) * 8 + 4096
     times, walls, last = [], [], None
-    nrep = max(2, min(3, a.repeats))  # whole-program runs; the first one also warms driver + page cache
+    clk = None
+    if rank == 0:
+        try:  # SM clocks and throttle reasons while the reference runs (plain-Python NVML sampler, loaded by
+            # path so that nothing else of the repo's package is imported into this arm)
+            import importlib.util
+            spec = importlib.util.spec_from_file_location(
+                "w3d_clocks", os.path.join(os.path.dirname(HERE), "3d-wave-equation-mpi-cuda_b200", "utils", "clocks.py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            clk = mod.ClockSampler(0, 0.02)
+            clk.__enter__()
+        except Exception:  # noqa: BLE001
+            clk = None
+    # whole-program runs: one untimed run (driver, page cache, the W warm-up steps) and then the timed ones;
+    # the median is reported, the same statistic as our arm
+    nrep = 1 + max(1, min(3, a.repeats))
     err = None
     for rep in range(nrep):
         r = run_program("cuda_sol", argv, nranks=ws, rank=rank, job=f"{job}_{rep}", cwd=work,
@@ -144,35 +187,58 @@ def bench(a, tau: float):
             dist.barrier()
     if ws > 1:
         import torch.distributed as dist
-        flag = [err]
         gathered = [None] * ws
         dist.all_gather_object(gathered, err)
         err = next((g for g in gathered if g), None)
         dist.destroy_process_group()
+    clocks = {}
+    if clk is not None:
+        clk.__exit__(None, None, None)
+        clocks = clk.summary()
     if err:
         emit({"impl": "reference", "unavailable": err.replace("\n", " ")[:400]})
         return
     if rank == 0:
-        t_ms = min(times[1:]) if len(times) > 1 else times[0]
+        import statistics
+        timed = times[1:] if len(times) > 1 else times
+        t_ms = statistics.median(timed)
         cells = float(N + 1) ** 3
         ea, er, extras = last
-        emit({
+        dims = dims_create(ws)
+        out = {
             "metric": "Gcell-updates/s (device-timed, max over ranks)", "value": cells * K / (t_ms * 1e-3) / 1e9,
             "unit": "Gcell-updates/s", "n_gpus": a.gpus, "steps": K, "warmup": a.warmup, "ms_per_step": t_ms / K,
             "higher_is_better": True, "scaling": getattr(a, "scaling", "strong"), "vs_baseline": None, "dtype": "fp64",
             "data": "synthetic (analytic initial condition)", "impl": "reference",
-            "config": {"model": f"cuda_sol N={N} L={L} tau={tau} timesteps={K}", "global_batch": int(cells), "seq_len": K,
-                       "parallelism": f"{ws} MPI ranks (MPI_Dims_create grid), 1 rank per GPU",
+            "config": problem_config(N, L, tau, K, dims, cells),
+            "detail": {"program": "baseline/_ref/bin/cuda_sol (unmodified reference sources, ARCH=sm_100a)",
+                       "ranks": f"{ws} MPI ranks (MPI_Dims_create grid), 1 rank per GPU",
                        "transport": "MPI stand-in (baseline/mpi_shim/mpi.h: shared-memory mailboxes); host-staged faces "
                                     "as in the reference",
-                       "timer": "reference's own rank-0 cudaEvent pair ('numerical solution calculated in'); best of "
-                                f"{len(times) - 1 if len(times) > 1 else 1} whole-program runs after one warm-up run",
-                       "solve_ms_all": times, "shim_wall_ms_max_over_ranks": walls,
+                       "timer": "reference's own rank-0 cudaEvent pair ('numerical solution calculated in'); median of "
+                                f"{len(timed)} whole-program runs after one warm-up run",
+                       "repeats": len(timed), "solve_ms_all": times, "shim_wall_ms_max_over_ranks": walls,
                        "reference_timers_ms": extras,
                        "max_abs_error_last_layer": ea[-1] if ea else None,
                        "max_rel_error_last_layer": er[-1] if er else None},
+            "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
+                       "reasons": clocks.get("reasons", []), "samples": clocks.get("samples"),
+                       "note": "sampled over the whole-program runs (process start-up and allocation included)"},
             "gpu_launches": None,
-        })
+        }
+        # End to end: the reference's timed region IS its end-to-end path — every step stages the faces and the
+        # block maxima through pinned host memory and syncs the host (ref: cuda_sol.cpp:382-428). The MPI
+        # stand-in clocks the same region on every rank (first MPI_Barrier -> first MPI_Reduce); max over ranks.
+        wt = [w for w in (walls[1:] if len(walls) > 1 else walls) if w == w and w > 0]
+        if wt:
+            w_ms = statistics.median(wt)
+            h2d, d2h = staged_bytes_per_step(N, dims)
+            out["e2e"] = {"value": cells * K / (w_ms * 1e-3) / 1e9, "unit": "Gcell-updates/s", "ms_per_step": w_ms / K,
+                          "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                          "note": "wall clock of the reference's whole solve (first MPI_Barrier -> first MPI_Reduce), max "
+                                  "over ranks, measured by the MPI stand-in; per step it copies six padded faces each way "
+                                  "through pinned host memory plus two block-maxima arrays device->host; bytes are per rank"}
+        emit(out)
     shutil.rmtree(work, ignore_errors=True)
 
 

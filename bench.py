@@ -44,6 +44,32 @@ def world():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 
 
+def problem_config(N, L, tau, K, dims, cells):
+    """The part of `config` that names the problem; both arms print exactly this (arm-specific detail such
+    as transport, tile plan and timer lives under `detail`)."""
+    ng = max(1, dims[0] * dims[1] * dims[2])
+    return {"model": f"wave3d N={N} L={L} tau={tau} timesteps={K}", "global_batch": int(cells), "seq_len": K,
+            "parallelism": "x".join(str(d) for d in dims),
+            "l2": "inputs larger than L2 (one fp64 layer = %.0f MB per GPU)" % (cells * 8 / 1e6 / ng),
+            "stat": "median of the timed solves"}
+
+
+NVLINK_GBS_MEASURED = 770.0  # peer copy per direction per GPU on this pool (B200_PROFILING.md); nominal 900
+
+
+def halo_bytes_per_step(N, dims):
+    """Bytes one rank sends to OTHER ranks per step (max over ranks): every owned face cell that has a
+    neighbour rank is stored once into that neighbour's ghost layer (8 B). The periodic wrap inside one
+    box and the Dirichlet walls send nothing."""
+    from wave3d_b200.parallel.decomp import Decomposition
+    dec = Decomposition(N, tuple(dims))
+    worst = 0
+    for r in range(dec.nranks):
+        b, fe = dec.box(r), dec.face_elems(r)
+        worst = max(worst, sum(8 * fe[f] for f in range(6) if b.nbr[f] >= 0 and b.nbr[f] != r))
+    return worst
+
+
 def flush_l2(torch, dev):
     # write a buffer larger than the 126 MB L2 between timed solves (inputs are >> L2 anyway at N=512)
     buf = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=dev)
@@ -111,64 +137,67 @@ def run_ours(a):
     e2e, e2e_error = None, None
     if not a.no_e2e and (transport == "peer" or not distributed):
         try:
-            # WaveSolver.run_streamed: per layer H2D of the step descriptor (pinned), fused kernel, D2H of the
-            # layer's maxima; the host reads layer n while layer n+1 runs (lag 1). lag 0 = wait for every layer.
+            # run_streamed (WaveSolver / DistributedWaveSolver): per layer H2D of the step descriptor (pinned),
+            # fused kernel, D2H of the layer's maxima; the host reads layer n while layer n+1 runs (lag 1).
+            # lag 0 = wait for every layer. Distributed: maxima and wall time are reduced with MAX over ranks.
             desc = inner.make_descriptors()
+
             def streamed(lag):
                 ts = []
                 for rep in range(3):
-                    if distributed:
-                        solver._reset()
-                    else:
+                    if not distributed:
                         solver.reset()
                     barrier()
-                    r = inner.run_streamed(desc, lag=lag)
+                    r = solver.run_streamed(desc, lag=lag)
                     barrier()
                     ts.append(r.solve_ms)
-                t = statistics.median(ts[1:])
-                if distributed:
-                    tt = torch.tensor([t], dtype=torch.float64, device=dev)
-                    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-                    t = float(tt.item())
-                return t, r
+                return statistics.median(ts[1:]), r
             t_e2e, r_e2e = streamed(1)
             t_sync, _ = streamed(0)
-            assert r_e2e.max_abs[-1] == res.max_abs[-1] or distributed  # same solve (local maxima under torchrun)
+            # the streamed solve is the same solve: identical maxima on every layer (max over ranks on both sides)
+            same = r_e2e.max_abs == res.max_abs and r_e2e.max_rel == res.max_rel
             ml = bool(r_e2e.extra.get("multi_layer_launch"))
             e2e = {"value": cells * K / (t_e2e * 1e-3) / 1e9, "unit": "Gcell-updates/s",
                    "h2d_bytes_per_step": r_e2e.extra["h2d_bytes_per_step"], "d2h_bytes_per_step": r_e2e.extra["d2h_bytes_per_step"],
                    "ms_per_step": t_e2e / K, "lag_layers": 1, "multi_layer_launch": ml,
-                   "sync_value": cells * K / (t_sync * 1e-3) / 1e9,
-                   "note": ("WaveSolver.run_streamed, small-box path: layers 2..T run in the persistent multi-layer launch; every "
+                   "sync_value": cells * K / (t_sync * 1e-3) / 1e9, "maxima_equal_device_timed_solve": bool(same),
+                   "note": ("run_streamed, small-box path: layers 2..T run in the persistent multi-layer launch; every "
                             "layer's step descriptor is copied pinned->device on a copy stream while the kernel runs (the "
                             "kernel waits for it), every layer's max abs/rel error is written to mapped pinned host memory "
                             "with a ready flag that the host polls. " if ml else
-                            "WaveSolver.run_streamed: every layer copies its step descriptor pinned->device, runs the fused "
+                            "run_streamed: every layer copies its step descriptor pinned->device, runs the fused "
                             "kernel and copies its max abs/rel error device->host; the host reads layer n while layer n+1 "
                             "runs (sync_value: host waits for every layer before launching the next). ") +
                            "Wall clock incl. layer 0, max over ranks; bytes are per rank"}
         except Exception as ex:  # noqa: BLE001 — the device-timed line must still be printed
             e2e_error = f"{type(ex).__name__}: {ex}"[:300]
-    # roofline: 24 B of HBM traffic per cell per step (read u^{n-1}, read u^{n-2}, write u^n) against the
-    # MEASURED copy bandwidth of this pool (MEASURED_PEAKS.json; fallback 6650 GB/s, B200_PROFILING.md)
+    # roofline: the slower of (a) 24 B of HBM traffic per cell per step (read u^{n-1}, read u^{n-2}, write u^n)
+    # against the MEASURED copy bandwidth of this pool (MEASURED_PEAKS.json; fallback 6650 GB/s,
+    # B200_PROFILING.md) and (b) the halo bytes a rank pushes over NVLink against the measured 770 GB/s
     hbm, src = 6650.0, "fallback"
     try:
         hbm, src = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
     except Exception:  # noqa: BLE001
         pass
-    roof = a.gpus * hbm / 24.0
-    roofline = {"bytes_per_cell_step": 24, "hbm_gbs_per_gpu": hbm, "basis": f"of {src}", "roofline_gcells": roof,
-                "fraction": value / roof}
+    dims_used = tuple(res.dims) if res else (1, 1, 1)
+    halo = halo_bytes_per_step(N, dims_used)
+    t_hbm = cells / a.gpus * 24.0 / (hbm * 1e9)   # seconds per step, HBM term (per GPU)
+    t_nvl = halo / (NVLINK_GBS_MEASURED * 1e9)     # seconds per step, NVLink term (per GPU, one direction)
+    roof = cells / max(t_hbm, t_nvl) / 1e9
+    roofline = {"bytes_per_cell_step": 24, "hbm_gbs_per_gpu": hbm, "basis": f"of {src}",
+                "halo_bytes_per_step": halo, "nvlink_gbs_per_gpu": NVLINK_GBS_MEASURED,
+                "hbm_us_per_step": t_hbm * 1e6, "nvlink_us_per_step": t_nvl * 1e6,
+                "bound": "hbm" if t_hbm >= t_nvl else "nvlink",
+                "roofline_gcells": roof, "fraction": value / roof}
     out = {
         "metric": "Gcell-updates/s (device-timed, max over ranks)", "value": value, "unit": "Gcell-updates/s",
         "n_gpus": a.gpus, "steps": K, "warmup": a.warmup, "ms_per_step": t_ms / K, "higher_is_better": True,
         "scaling": a.scaling, "vs_baseline": None, "dtype": "fp64", "data": "synthetic (analytic initial condition)",
         "impl": "ours",
-        "config": {"model": f"wave3d N={N} L={a.length} tau={TAU} timesteps={K}", "global_batch": int(cells),
-                   "seq_len": K, "parallelism": "x".join(str(d) for d in (res.dims if res else (1, 1, 1))),
-                   "transport": transport, "l2": "inputs larger than L2 (2 fields x %.0f MB per GPU) + 256 MB flush "
-                   "between timed solves" % (cells * 8 / 1e6 / max(1, a.gpus)),
-                   "repeats": len(times), "stat": "median", "solve_ms_all": [round(t, 4) for t in times],
+        "config": problem_config(N, a.length, TAU, K, dims_used, cells),
+        "detail": {"transport": transport, "l2_flush": "256 MB buffer written between timed solves",
+                   "repeats": len(times), "solve_ms_all": [round(t, 4) for t in times],
+                   "multi_layer_launch": bool(inner.multistep_active),
                    "plan": res.extra.get("plan") if res else None,
                    "max_abs_error_last_layer": res.max_abs[-1] if res else None,
                    "max_rel_error_last_layer": res.max_rel[-1] if res else None},
@@ -200,7 +229,7 @@ def run_reference(a):
         if rank == 0:
             print(json.dumps({"impl": "reference", "unavailable": f"baseline/run_reference.py not importable: {e}"}))
         return
-    rr.bench(a, TAU)
+    rr.bench(a, TAU, problem_config)
 
 
 if __name__ == "__main__":

@@ -252,6 +252,12 @@ __device__ __noinline__ void push_row_x(const StepParams& p, int w, int i, int j
 
 // Optional per-CTA phase timestamps of the last k_step launch (WAVE3D_DBG_TS=1; scripts/cta_timeline.py)
 __device__ unsigned long long g_dbg_ts[2048 * 8];
+// Per-CTA phase accumulators (SM clock cycles) of the last launch, same switch: producer lane
+// [0] item fetch (queue atomic), [1] dependency poll, [2] acquire fences, [3] waits for a free ring slot,
+// [4] publishing finished items, [5] items, [6] items that had to wait, [7] poll cycles of rank-face items,
+// [8] rank-face items, [9] kernel cycles; compute warp 0: [10] waits for the next item id, [11] waits for
+// the first two planes of an item, [12] waits for planes inside the march, [13] item set-up, [14] march.
+__device__ unsigned long long g_dbg_acc[2048 * 16];
 
 constexpr int kMaxWarps = 7;    // compute warps per CTA (one more warp is the TMA producer): 256 threads, 2 CTAs per SM
 constexpr int kTZ = 64;         // tile width in z: one warp row = 32 lanes x 2 cells
@@ -326,6 +332,9 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
     if (warp == ncw) {
         // ================= producer warp: one lane feeds both rings with TMA =================
         if (lane == 0) {
+            long long a_q = 0, a_poll = 0, a_acq = 0, a_slot = 0, a_pub = 0, a_pollf = 0;
+            unsigned a_items = 0, a_waited = 0, a_fitems = 0;
+            const long long a_t0 = dbg ? clock64() : 0;
             // Neighbours must have finished the previous layer: their ghost stores are complete (RAW)
             // and they no longer read the ghosts this layer overwrites (WAR). Nothing of this CTA
             // touches global memory before its first plane has arrived, i.e. after this wait.
@@ -355,6 +364,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             int pub_kq = 0, issued_kq = 0;
             int pub_gid[8];
             auto publish = [&](bool block) {
+                const long long c0 = dbg ? clock64() : 0;
                 while (MULTI && pub_kq < issued_kq) {
                     const uint32_t bar = pbar + 8u * (pub_kq & 7), par = (uint32_t)((pub_kq >> 3) & 1);
                     if (block) mbar_wait(bar, par);
@@ -399,12 +409,15 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     }
                     pub_kq++;
                 }
+                if (dbg) a_pub += clock64() - c0;
             };
             for (int kq = 0;; kq++) {
                 // the first item is the CTA's own index (no atomic on the critical path), later ones
                 // come from the queue, which starts at gridDim.x
+                const long long cq0 = dbg ? clock64() : 0;
                 int gid = kq == 0 ? (int)blockIdx.x : (int)(gridDim.x + atomicAdd(&p.scratch[2], 1u));
                 if (gid >= ntotal) gid = -1;
+                if (dbg) a_q += clock64() - cq0;
                 s_item[kq & 7] = gid;
                 mbar_arrive(ibar + 8u * (kq & 7));  // release: the compute warps read s_item after this phase
                 if (gid < 0) {
@@ -456,13 +469,20 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     if (tyi == p.nty - 1 && p.flag_in[3]) { wp[nw] = p.flag_in[3]; wn[nw++] = needf; }
                     if (tzi == 0 && p.flag_in[4]) { wp[nw] = p.flag_in[4]; wn[nw++] = needf; }
                     if (tzi == p.ntz - 1 && p.flag_in[5]) { wp[nw] = p.flag_in[5]; wn[nw++] = needf; }
+                    if (dbg) {
+                        a_items++;
+                        if (nw > nepoch) a_fitems++;
+                    }
                     if (nw) {
                         const unsigned long long t0 = globaltimer_ns();
+                        const long long cp0 = dbg ? clock64() : 0;
+                        bool waited = false;
                         for (;;) {
                             bool ok = true;
                             for (int q = 0; q < nw; q++)
                                 ok = ok && (*reinterpret_cast<const volatile uint32_t*>(wp[q]) >= wn[q]);
                             if (ok) break;
+                            waited = true;
                             publish(false);  // never sit on finished items while waiting for somebody else's
                             __nanosleep(32);
                             if (globaltimer_ns() - t0 > p.timeout_ns) {
@@ -473,8 +493,15 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                         // acquire side: one gpu-scope fence for all epoch words (seven dependent acquire
                         // loads cost ~5 us per item); the few rank-face items re-read their flag words with
                         // a system-scope acquire load
+                        const long long cp1 = dbg ? clock64() : 0;
                         if (nepoch) __threadfence();
                         for (int q = nepoch; q < nw; q++) (void)ld_acquire_sys(wp[q]);
+                        if (dbg) {
+                            a_poll += cp1 - cp0;
+                            if (nw > nepoch) a_pollf += cp1 - cp0;
+                            a_acq += clock64() - cp1;
+                            a_waited += waited ? 1u : 0u;
+                        }
                     }
                     asm volatile("fence.proxy.async;" ::: "memory");
                 }
@@ -485,22 +512,35 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                 for (int q = 0; q < nplanes + 2; q++) {
                     // source plane seq q = owned plane xa-1+q = storage plane xa+q
                     publish(false);
+                    const long long cs0 = dbg ? clock64() : 0;
                     mbar_wait(empty1 + 8u * s1i, ph1);
+                    if (dbg) a_slot += clock64() - cs0;
                     mbar_expect_tx(full1 + 8u * s1i, box1_bytes);
                     tma_load_3d(ring1 + (uint32_t)s1i * slot1_bytes, msrc, c0_src, c1_src, xa + q, full1 + 8u * s1i);
                     if (++s1i == p.s1) { s1i = 0; ph1 ^= 1; }
                     if (!FIRST && q >= 2) {
                         // in-place plane of iteration q-2 = owned plane xa+q-2 = storage plane xa+q-1
+                        const long long cs1 = dbg ? clock64() : 0;
                         mbar_wait(empty0 + 8u * s0i, ph0);
+                        if (dbg) a_slot += clock64() - cs1;
                         mbar_expect_tx(full0 + 8u * s0i, box0_bytes);
                         tma_load_3d(ring0 + (uint32_t)s0i * slot0_bytes, mio, c0_io, c1_io, xa + q - 1, full0 + 8u * s0i);
                         if (++s0i == p.s0) { s0i = 0; ph0 ^= 1; }
                     }
                 }
             }
+            if (dbg) {
+                unsigned long long* acc = g_dbg_acc + (size_t)blockIdx.x * 16;
+                acc[0] = (unsigned long long)a_q; acc[1] = (unsigned long long)a_poll; acc[2] = (unsigned long long)a_acq;
+                acc[3] = (unsigned long long)a_slot; acc[4] = (unsigned long long)a_pub; acc[5] = a_items;
+                acc[6] = a_waited; acc[7] = (unsigned long long)a_pollf; acc[8] = a_fitems;
+                acc[9] = (unsigned long long)(clock64() - a_t0);
+            }
         }
     } else {
         // ================================ compute warps ================================
+        long long b_item = 0, b_first = 0, b_full = 0, b_setup = 0, b_march = 0;
+        const bool dbgw = dbg && tid == 0;
         double cosn = s_bcast[0], rcos = s_bcast[1];
         double coef = s_bcast[2];
         const double hx2 = p.hx2, hy2 = p.hy2, hz2 = p.hz2, rx = p.rx, ry = p.ry, rz = p.rz;
@@ -516,7 +556,10 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
         int cur_n = -1;
 
         for (int kq = 0;; kq++) {
+            const long long ci0 = dbgw ? clock64() : 0;
             mbar_wait(ibar + 8u * (kq & 7), (uint32_t)((kq >> 3) & 1));
+            const long long ci1 = dbgw ? clock64() : 0;
+            if (dbgw) b_item += ci1 - ci0;
             const int gid = s_item[kq & 7];
             if (gid < 0) break;
             const int n = p.n0 + (MULTI ? gid / nitems : 0);
@@ -609,6 +652,8 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             const double rsz0 = vk0 ? p.rsz[kk] : 0.0, rsz1 = vk1 ? p.rsz[kk + 1] : 0.0;
 
             // first two source planes of the segment
+            const long long cf0 = dbgw ? clock64() : 0;
+            if (dbgw) b_setup += cf0 - ci1;
             mbar_wait(full1 + 8u * fi, fph);
             uint32_t am = ring1 + (uint32_t)fi * slot1_bytes;
             if (++fi == p.s1) { fi = 0; fph ^= 1; }
@@ -617,8 +662,11 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
             if (++fi == p.s1) { fi = 0; fph ^= 1; }
 
             if (dbg && tid == 0 && kq == 0) g_dbg_ts[blockIdx.x * 8 + 2] = globaltimer_ns();  // first data is here
+            const long long cm0 = dbgw ? clock64() : 0;
+            if (dbgw) b_first += cm0 - cf0;
             for (int t = 0; t < nplanes; t++) {
                 const int i = xa + t;  // owned x index of the centre plane
+                const long long cw0 = dbgw ? clock64() : 0;
                 mbar_wait(full1 + 8u * fi, fph);
                 const uint32_t ap = ring1 + (uint32_t)fi * slot1_bytes;
                 if (++fi == p.s1) { fi = 0; fph ^= 1; }
@@ -627,6 +675,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                     mbar_wait(full0 + 8u * f0i, f0ph);
                     a0 = ring0 + (uint32_t)f0i * slot0_bytes;
                 }
+                if (dbgw) b_full += clock64() - cw0;
 
                 const bool ei = i >= p.elo0 && i <= p.ehi0;
                 const double cs = __dmul_rn(cosn, __ldg(p.sx + i));
@@ -698,6 +747,7 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
                 am = ac;
                 ac = ap;
             }
+            if (dbgw) b_march += clock64() - cm0;
             // the last two source planes of the segment are no longer needed either
             __syncwarp();
             if (lane == 0) {
@@ -725,6 +775,11 @@ __global__ void __launch_bounds__((kMaxWarps + 1) * 32, 2) k_step(const __grid_c
         }
 
         if (dbg && tid == 0) g_dbg_ts[blockIdx.x * 8 + 3] = globaltimer_ns();
+        if (dbgw) {
+            unsigned long long* acc = g_dbg_acc + (size_t)blockIdx.x * 16;
+            acc[10] = (unsigned long long)b_item; acc[11] = (unsigned long long)b_first; acc[12] = (unsigned long long)b_full;
+            acc[13] = (unsigned long long)b_setup; acc[14] = (unsigned long long)b_march;
+        }
         // ---- error maxima: warp -> CTA
         const double wa = warp_max(ea.mabs), wr = warp_max(ea.mrel);
         if (lane == 0) {
@@ -1392,6 +1447,15 @@ extern "C" int wave3d_debug_copy_timestamps(unsigned long long* host, int nctas)
     if (nctas > 2048) nctas = 2048;
     W3D_TRY(cudaDeviceSynchronize());
     W3D_TRY(cudaMemcpyFromSymbol(host, g_dbg_ts, sizeof(unsigned long long) * 8 * (size_t)nctas));
+    return 0;
+}
+
+extern "C" int wave3d_debug_copy_phases(unsigned long long* host, int nctas, int device) {
+    using namespace w3d;
+    if (nctas > 2048) nctas = 2048;
+    if (device >= 0) W3D_TRY(cudaSetDevice(device));
+    W3D_TRY(cudaDeviceSynchronize());
+    W3D_TRY(cudaMemcpyFromSymbol(host, g_dbg_acc, sizeof(unsigned long long) * 16 * (size_t)nctas));
     return 0;
 }
 
