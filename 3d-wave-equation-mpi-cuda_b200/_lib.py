@@ -46,11 +46,14 @@ class Timings(C.Structure):
                 ("exchange_ms", C.c_double), ("hostdev_ms", C.c_double), ("error_ms", C.c_double)]
 
 
+MAX_CHUNKS = 32  # WAVE3D_MAX_CHUNKS
+
+
 class Plan(C.Structure):
     _fields_ = [("tz", C.c_int32), ("ty", C.c_int32), ("rj", C.c_int32), ("warps", C.c_int32),
                 ("nty", C.c_int32), ("ntz", C.c_int32), ("nchunks", C.c_int32), ("s1", C.c_int32), ("s0", C.c_int32),
                 ("smem_bytes", C.c_int32), ("ctas", C.c_int32), ("slots", C.c_int32), ("efficiency", C.c_double),
-                ("xcut", C.c_int32 * 18), ("order", C.c_int32 * 16)]
+                ("xcut", C.c_int32 * (MAX_CHUNKS + 2)), ("order", C.c_int32 * MAX_CHUNKS)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("xcut", "order")}
@@ -75,7 +78,8 @@ class SolverOpts(C.Structure):
 class Export(C.Structure):
     _fields_ = [("ipc_handle", C.c_ubyte * 64), ("off_field", C.c_int64 * 2), ("off_flags", C.c_int64),
                 ("off_err", C.c_int64), ("slab_bytes", C.c_int64), ("layout", Layout), ("box", Box),
-                ("device", C.c_int32), ("pid", C.c_int32)]
+                ("device", C.c_int32), ("pid", C.c_int32), ("plan_nchunks", C.c_int32),
+                ("plan_xcut", C.c_int32 * (MAX_CHUNKS + 2)), ("reserved", C.c_int32)]
 
 
 SCRATCH_WORDS = 16
@@ -127,6 +131,7 @@ def _sig(lib):
         "wave3d_cuda_device_count": (i32, []),
         "wave3d_cuda_last_error": (cs, []),
         "wave3d_plan_make": (None, [B, i32, C.POINTER(Plan)]),
+        "wave3d_plan_make_style": (None, [B, i32, i32, C.POINTER(Plan)]),
         "wave3d_cuda_tables": (i32, [P, B, vp, vp, vp, vp, vp, vp, vp]),
         "wave3d_cuda_layer0": (i32, [P, B, L, vp, vp, vp, vp, vp]),
         "wave3d_cuda_step": (i32, [P, B, L, C.POINTER(Plan), C.POINTER(vp), vp, vp, i32, i32, C.POINTER(Peers), vp, vp,

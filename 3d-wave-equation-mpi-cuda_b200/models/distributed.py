@@ -43,6 +43,24 @@ class DistributedWaveSolver:
         # collectives run on the process group's native device
         self.coll_device = self.device if dist.get_backend() == "nccl" else torch.device("cpu")
         want_peer = transport in ("auto", "peer") and backend == "cuda"
+        # Ranks that share a GPU (more processes than devices, the reference's MPS launch mode, ref:
+        # cuda_sol.cpp:517-519): the fused kernels of two processes would spin on each other's flags while
+        # time-slicing one device, which can only progress through context switches (and can trip the GPU's
+        # watchdog). Such ranks exchange their faces with the staged transport instead — no kernel ever waits.
+        self.shared_gpu = False
+        if backend == "cuda":
+            import socket
+            pairs = [None] * self.world
+            dist.all_gather_object(pairs, (socket.gethostname(), self.dev_index))
+            self.shared_gpu = len(set(pairs)) < len(pairs)
+        if self.shared_gpu and want_peer:
+            if transport == "peer":
+                raise RuntimeError(
+                    f"wave3d: {self.world} ranks on {len(set(pairs))} GPU(s): the peer transport needs one GPU per "
+                    "process (its kernels wait for each other inside the GPU). Use transport='staged' (or 'auto'), "
+                    "or drive several ranks from ONE process: WaveSolver(problem, nranks=..., devices=[...])")
+            warnings.warn("wave3d: several ranks share a GPU: using the staged halo transport (no in-kernel waits)")
+            want_peer = False
         self.transport = "peer" if want_peer else "staged"
         mk = lambda tr: WaveSolver(problem, nranks=self.world, dims=dims, backend=backend, transport=tr,
                                    devices=[self.dev_index] if backend == "cuda" else None, use_graph=use_graph,
@@ -72,6 +90,7 @@ class DistributedWaveSolver:
             if self.backend == "cuda":
                 torch.cuda.synchronize(self.device)
             dist.barrier()
+            self.halo = None  # pinned / device staging buffers go before the solver and the CUDA context
             self.inner.close()
             self.inner = None
 

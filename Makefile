@@ -18,7 +18,7 @@ build/%.o: csrc/%.cpp include/wave3d.h
 	@mkdir -p build
 	$(HOST_COMP) $(CXXFLAGS) -c $< -o $@
 
-build/%.o: csrc/%.cu include/wave3d.h csrc/wave3d_internal.hpp
+build/%.o: csrc/%.cu include/wave3d.h csrc/wave3d_internal.hpp $(wildcard csrc/*.inc)
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@ 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; false)
 

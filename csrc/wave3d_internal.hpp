@@ -45,6 +45,8 @@ struct StepLaunch {
     uint32_t* epoch;     // multi-layer launches: one word per (tile, chunk) item, zeroed before the solve
     uint32_t* stepdone;  // multi-layer launches: 3*(timesteps+2) words (items per layer, then x-face items
                          // per layer and side), zeroed before the solve
+    uint32_t* chunkdone; // multi-layer launches: 8 * 4 * WAVE3D_MAX_CHUNKS words (y/z face strips done per x-chunk)
+    int yz_chunk_flags;  // y/z neighbours use the same x-cuts: hand-shake per (face, x-chunk)
     const double* desc;  // device pointer to {arg_t, coef} or nullptr
     // streamed multi-layer launch: descriptor table in device memory (NaN until uploaded), mapped host
     // memory for the layer maxima and their ready flags

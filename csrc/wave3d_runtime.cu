@@ -28,6 +28,10 @@ void set_err(char* err, size_t errlen, const std::string& s) {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+constexpr size_t kFlagBytes = 1024;  // 6 inbound flag blocks of WAVE3D_FLAG_WORDS epoch words
+static_assert(6 * WAVE3D_FLAG_WORDS * 4 <= kFlagBytes, "flag blocks");
+constexpr size_t kChunkdoneBytes = 8 * 4 * WAVE3D_MAX_CHUNKS * 4;
+
 struct Rank {
     int rank = 0, local = 0, device = -1;
     wave3d_box box;
@@ -38,7 +42,10 @@ struct Rank {
     size_t slab_bytes = 0;
     size_t off_field[2] = {0, 0}, off_tabs[6] = {0}, off_err = 0, off_flags = 0, off_scratch = 0, off_desc = 0,
            off_ferr = 0, off_epoch = 0, off_stepdone = 0;
+    size_t off_chunkdone = 0;
     size_t epoch_bytes = 0, stepdone_bytes = 0;
+    uint32_t* chunkdone = nullptr; // multi-layer launch: y/z face strips done per (layer & 7, face, x-chunk)
+    bool yz_chunk_flags = false;   // every y/z neighbour cuts x like this rank: per-chunk hand-shake is possible
     uint32_t* epoch = nullptr;     // multi-layer launch: last completed layer per (tile, chunk) item
     uint32_t* stepdone = nullptr;  // multi-layer launch: completed items per layer
     uint64_t* ferr_scratch = nullptr;  // scratch of the stand-alone error evaluation (zeroed with the slab)
@@ -115,7 +122,7 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     r.off_err = off;
     off += align_up((size_t)(s->prob.timesteps + 1) * 16, 256);
     r.off_flags = off;
-    off += 256;
+    off += kFlagBytes;
     r.off_scratch = off;
     off += 256;
     r.off_desc = off;
@@ -128,6 +135,8 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     r.off_stepdone = off;
     r.stepdone_bytes = align_up((size_t)(s->prob.timesteps + 2) * 4 * 3, 256);
     off += r.stepdone_bytes;
+    r.off_chunkdone = off;  // directly behind stepdone: one memset clears epoch + stepdone + chunkdone
+    off += kChunkdoneBytes;
     r.slab_bytes = off;
     W3D_TRY(cudaMalloc(&r.slab, r.slab_bytes));
     W3D_TRY(cudaMemsetAsync(r.slab, 0, r.slab_bytes, stream_of(s, r)));
@@ -141,6 +150,7 @@ int alloc_rank_cuda(wave3d_solver* s, Rank& r) {
     r.epoch = reinterpret_cast<uint32_t*>(r.slab + r.off_epoch);
     r.ferr_scratch = reinterpret_cast<uint64_t*>(r.slab + r.off_ferr);
     r.stepdone = reinterpret_cast<uint32_t*>(r.slab + r.off_stepdone);
+    r.chunkdone = reinterpret_cast<uint32_t*>(r.slab + r.off_chunkdone);
     for (int w = 0; w < 2; w++) {
         if (encode_field_map(&r.map_halo[w], r.field[w], &r.lay, r.plan.tz + 4, r.plan.ty + 2)) return -1;
         if (encode_field_map(&r.map_core[w], r.field[w], &r.lay, r.plan.tz, r.plan.ty)) return -1;
@@ -204,11 +214,21 @@ void wire_rank(wave3d_solver* s, Rank& r, const std::vector<unsigned char*>& bas
             if (q < 0) continue;
             double* qfield = reinterpret_cast<double*>(base[q] + ex[q].off_field[w]);
             ghost_target(ex[q].box, ex[q].layout, qfield, f, &P.dst[f], &P.sa[f], &P.sb[f]);
-            P.flag_out[f] = reinterpret_cast<uint32_t*>(base[q] + ex[q].off_flags) + (f ^ 1);
-            P.flag_in[f] = r.flags + f;
+            P.flag_out[f] = reinterpret_cast<uint32_t*>(base[q] + ex[q].off_flags) + (f ^ 1) * WAVE3D_FLAG_WORDS;
+            P.flag_in[f] = r.flags + f * WAVE3D_FLAG_WORDS;
         }
         if (r.rank != 0 && base[0]) P.root_err = reinterpret_cast<uint64_t*>(base[0] + ex[0].off_err);
     }
+    // y/z neighbours that cut x exactly like this rank can hand-shake per (face, x-chunk)
+    r.yz_chunk_flags = true;
+    for (int f = 2; f < 6; f++) {
+        const int q = r.box.nbr[f];
+        if (q < 0) continue;
+        bool same = ex[q].plan_nchunks == r.plan.nchunks;
+        for (int c = 0; same && c <= r.plan.nchunks; c++) same = ex[q].plan_xcut[c] == r.plan.xcut[c];
+        if (!same) r.yz_chunk_flags = false;
+    }
+    if (const char* e = getenv("WAVE3D_YZ_CHUNK_FLAGS")) r.yz_chunk_flags = r.yz_chunk_flags && atoi(e) != 0;
     (void)s;
 }
 
@@ -223,6 +243,8 @@ void fill_export(const wave3d_solver* s, const Rank& r, wave3d_export* out) {
     out->box = r.box;
     out->device = r.device;
     out->pid = (int)getpid();
+    out->plan_nchunks = r.plan.nchunks;
+    for (int c = 0; c <= r.plan.nchunks && c < WAVE3D_MAX_CHUNKS + 2; c++) out->plan_xcut[c] = r.plan.xcut[c];
     (void)s;
 }
 
@@ -274,6 +296,8 @@ void fill_launch(wave3d_solver* s, Rank& r, StepLaunch& a) {
     a.scratch = r.scratch;
     a.epoch = r.epoch;
     a.stepdone = r.stepdone;
+    a.chunkdone = r.chunkdone;
+    a.yz_chunk_flags = r.yz_chunk_flags ? 1 : 0;
     a.spin_timeout_s = s->opts.spin_timeout_s;
     a.div_mode = s->div_mode;
     a.stream = stream_of(s, r);
@@ -349,7 +373,15 @@ bool multistep_ok(const wave3d_solver* s) {
 
 // ------------------------------------------------------------------- planner
 
-extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan) {
+// Boxes below this size run layers 2..T in the persistent multi-layer launch (measured on B200: below
+// ~50 M cells per rank the launch gap, pipeline fill and kernel tail of one launch per layer dominate).
+static bool small_box(const wave3d_box* b) { return (double)b->n[0] * b->n[1] * b->n[2] <= 48e6; }
+
+// style 0: guided chunk lengths (one launch per layer: long chunks first, short ones last, so that the
+//          end of every launch is balanced); style 1: equal chunks of ~16 planes (multi-layer launch: no
+//          per-layer tail to balance, fine items keep the dataflow between layers loose, and every rank
+//          with the same x extent cuts x the same way, which the per-chunk y/z hand-shake needs).
+extern "C" void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, wave3d_plan* plan) {
     memset(plan, 0, sizeof *plan);
     if (sms <= 0) sms = 148;
     const int ny = b->hi[1] - b->lo[1] + 1, nz = b->hi[2] - b->lo[2] + 1, X = b->n[0];
@@ -360,14 +392,18 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
     int ov[5] = {0, 0, 0, 0, 0};
     int nov = 0;
     if (const char* e = getenv("WAVE3D_TILE")) nov = sscanf(e, "%d,%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3], &ov[4]);
-    for (int rj = 1; rj <= 4; rj *= 2) {
+    int chunk_len = 16;
+    if (const char* e = getenv("WAVE3D_CHUNK")) chunk_len = std::max(2, atoi(e));
+    for (int rj = 1; rj <= 2; rj *= 2) {
         for (int warps = 2; warps <= 7; warps++) {
             const int ty = rj * warps;
             if (nov >= 2 && (ty != ov[0] || rj != ov[1])) continue;
+            // 6 source planes = 3 planes of look-ahead for the compute warps. Deeper rings put more rows of more
+            // planes in flight at the DRAM controllers and cost bandwidth (measured: 8/4 is 6 % slower than 6/4
+            // at N=512), shallower ones starve the compute warps.
             int s1 = nov >= 4 ? ov[3] : 6, s0 = nov >= 5 ? ov[4] : 4;
             int smem = plan_smem_bytes(ty, tz, s1, s0);
-            // keep two CTAs per SM when a shallower ring makes that possible
-            while (smem > 112 * 1024 && s1 > 4) {
+            while (smem > 106 * 1024 && s1 > 4) {  // keep two CTAs per SM (6 KB of static shared memory on top)
                 s1--;
                 if (s0 > 2) s0--;
                 smem = plan_smem_bytes(ty, tz, s1, s0);
@@ -382,29 +418,32 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
             const int nty = (ny + ty - 1) / ty;
             const int ntiles = nty * ntz;
             const int slots = sms * occ;
-            // Model (bandwidth bound, calibrated on B200): a CTA spends (planes + r0) plane-times per
-            // item, r0 = extra x-halo planes + segment set-up; CTAs work in rounds of `ctas` items, all
-            // CTAs of a round in the same x range. Losses: masked cells of ragged tiles, halo ring of the
-            // source boxes (L2 hits), RJ=1 spends more shared-memory traffic and instructions per cell,
-            // few warps per SM cannot cover the LDS/FP64 latencies, unfilled last round.
+            // Model (calibrated on B200): a CTA spends (planes + r0) plane-times per item, r0 = extra
+            // x-halo planes + item set-up. Losses: masked cells of ragged tiles, halo ring of the source
+            // boxes (L2 hits), RJ=1 spends more shared-memory traffic and instructions per cell, few warps
+            // per SM cannot cover the LDS/FP64 latencies, unfilled last round.
             const double waste = (double)nty * ty * ntz * tz / ((double)ny * nz);
             const double halo = (double)(ty + 2) * (tz + 4) / ((double)ty * tz) - 1.0;
-            const double rjf = rj == 1 ? 1.12 : (rj == 2 ? 1.0 : 1.08);
+            const double rjf = rj == 1 ? 1.12 : 1.0;
             const double occf = occ >= 2 ? 1.0 : 1.25;
             const int tlp = occ * warps;
             const double tlpf = tlp >= 14 ? 1.0 : 1.0 + 0.04 * (14 - tlp);
-            const double r0 = 1.5;  // plane-times lost per item: two extra x-halo planes + segment set-up
+            const double r0 = style ? 0.6 : 1.5;  // plane-times lost per item (look-ahead hides most of it)
             const int ctas = (int)std::min<int64_t>(slots, (int64_t)ntiles * std::max(1, X / 6));
-            // guided chunk lengths: start near 60 % of a CTA's share (never more than half a column),
-            // halve down to a floor that bounds the end-of-kernel imbalance
             const double share = (double)ntiles * X / ctas;
             int minlen = std::max(4, std::min(X, std::max(8, X / 32)));
             if (const char* e = getenv("WAVE3D_MINLEN")) minlen = std::max(2, std::min(X, atoi(e)));
-            int cuts[18], ord[16];
+            int cuts[WAVE3D_MAX_CHUNKS + 2], ord[WAVE3D_MAX_CHUNKS];
             int m = 0;
             cuts[0] = 0;
+            // the two end chunks must hold the seam planes (owned planes 1 and X-2): at least 2 planes each
+            const int mmax = std::max(1, std::min(WAVE3D_MAX_CHUNKS, X / 2));
             if (nov >= 3 && ov[2] > 0) {
-                m = std::min(16, std::min(ov[2], X));
+                m = std::min(mmax, ov[2]);
+                for (int c = 1; c <= m; c++) cuts[c] = (int)((int64_t)X * c / m);
+                for (int i = 0; i < m; i++) ord[i] = (i % 2 == 0) ? i / 2 : m - 1 - i / 2;
+            } else if (style) {
+                m = std::max(1, std::min(mmax, (X + chunk_len / 2) / chunk_len));
                 for (int c = 1; c <= m; c++) cuts[c] = (int)((int64_t)X * c / m);
                 for (int i = 0; i < m; i++) ord[i] = (i % 2 == 0) ? i / 2 : m - 1 - i / 2;
             } else {
@@ -431,7 +470,7 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
                 }
                 for (int c = 0; c < m; c++) cuts[c + 1] = cuts[c] + plen[c];
             }
-            const double tail = 0.5 * (cuts[ord[m - 1] + 1] - cuts[ord[m - 1]]) / std::max(1.0, share);
+            const double tail = style ? 0.0 : 0.5 * (cuts[ord[m - 1] + 1] - cuts[ord[m - 1]]) / std::max(1.0, share);
             const double fill = std::max(1.0, (double)slots / ((double)ntiles * m));
             const double eff = (double)X / (X + m * r0) / (1.0 + tail) / fill /
                                (waste * (1.0 + 0.3 * halo) * rjf * occf * tlpf);
@@ -447,6 +486,10 @@ extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan
             }
         }
     }
+}
+
+extern "C" void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan) {
+    wave3d_plan_make_style(b, sms, small_box(b) ? 1 : 0, plan);
 }
 
 // -------------------------------------------------------------------- solver
@@ -586,7 +629,7 @@ wave3d_solver* wave3d_solver_create(const wave3d_problem* p, const wave3d_solver
             if (use_device(r.device)) return fail("cudaSetDevice");
             cudaDeviceProp prop;
             if (check(cudaGetDeviceProperties(&prop, r.device), "props")) sms = prop.multiProcessorCount;
-            wave3d_plan_make(&r.box, sms, &r.plan);
+            wave3d_plan_make_style(&r.box, sms, multistep_ok(s) ? 1 : 0, &r.plan);
             if (r.plan.ty == 0) return fail("no feasible tile plan");
             if (alloc_rank_cuda(s, r)) return fail("allocation");
             if (wave3d_cuda_tables(&s->prob, &r.box, r.tabs[0], r.tabs[1], r.tabs[2], r.tabs[3], r.tabs[4], r.tabs[5],
@@ -705,9 +748,9 @@ int wave3d_solver_reset(wave3d_solver* s) {
         if (use_device(r.device)) return -1;
         cudaStream_t st = stream_of(s, r);
         W3D_TRY(cudaMemsetAsync(r.err, 0, (size_t)(s->prob.timesteps + 1) * 16, st));
-        W3D_TRY(cudaMemsetAsync(r.flags, 0, 256, st));
+        W3D_TRY(cudaMemsetAsync(r.flags, 0, kFlagBytes, st));
         W3D_TRY(cudaMemsetAsync(r.scratch, 0, 256, st));
-        W3D_TRY(cudaMemsetAsync(r.epoch, 0, r.epoch_bytes + r.stepdone_bytes, st));
+        W3D_TRY(cudaMemsetAsync(r.epoch, 0, r.epoch_bytes + r.stepdone_bytes + kChunkdoneBytes, st));
     }
     s->fresh = true;
     return wave3d_solver_sync(s);
@@ -1266,6 +1309,11 @@ int wave3d_main(int argc, const char* const* argv) {
     if (const char* e = getenv("WAVE3D_GRAPH")) o.use_graph = atoi(e);
     o.nranks = o.nlocal = nranks;
     o.first_rank = 0;
+    if (o.backend == WAVE3D_BACKEND_CUDA && ndev < 1) {
+        // WAVE3D_BACKEND=cuda forced on a box without a usable GPU
+        fprintf(stderr, "wave3d: no CUDA device available (backend=cuda); set WAVE3D_BACKEND=cpu for the CPU backend\n");
+        return 1;
+    }
     if (o.backend == WAVE3D_BACKEND_CUDA) {
         char host[256] = "localhost";
         gethostname(host, sizeof host);
@@ -1303,6 +1351,15 @@ int wave3d_main(int argc, const char* const* argv) {
         if (!rc) rc = wave3d_solver_sync(s);
         tm.solve_ms = tm.loop_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
     } else {
+        // ref: cuda_sol.cpp:338,385 prints "calculating layer n" before every layer. Here the host submits
+        // the whole solve at once (one CUDA graph or one persistent launch per GPU) and the device works
+        // through the layers on its own, so the lines mark submission, not completion; WAVE3D_PROGRESS=1
+        // gives the reference's lock-step behaviour, WAVE3D_QUIET=1 drops the lines.
+        const char* quiet = getenv("WAVE3D_QUIET");
+        if (!(quiet && atoi(quiet))) {
+            for (int n = 1; n <= p.timesteps; n++) printf("calculating layer %d\n", n);
+            fflush(stdout);
+        }
         rc = wave3d_solver_run(s, &tm);
     }
     if (rc) {

@@ -177,26 +177,31 @@ int wave3d_cuda_device_count(void);
 const char* wave3d_cuda_last_error(void);
 
 /* Tile plan of the fused kernel for one rank's box. */
+#define WAVE3D_MAX_CHUNKS 32 /* x-chunks per tile column */
+#define WAVE3D_FLAG_WORDS 40 /* epoch words per inbound face: [c] strip of x-chunk c (y/z faces), [WAVE3D_MAX_CHUNKS] whole layer */
 typedef struct wave3d_plan {
     int32_t tz;      /* tile width in z (cells) */
     int32_t ty;      /* tile height in y = rj * warps */
     int32_t rj;      /* rows per warp */
     int32_t warps;   /* warps per CTA */
     int32_t nty, ntz; /* tiles in y and z */
-    int32_t nchunks;  /* x-chunks per tile column (<= 16); items = nty*ntz*nchunks, handed out dynamically */
-    int32_t s1, s0;  /* ring depth: stencil-source planes / in-place planes */
+    int32_t nchunks;  /* x-chunks per tile column (<= WAVE3D_MAX_CHUNKS); items = nty*ntz*nchunks, handed out dynamically */
+    int32_t s1, s0;  /* ring depth: stencil-source planes (>= 4) / in-place planes */
     int32_t smem_bytes;
     int32_t ctas;    /* persistent CTAs pulling (tile, x-chunk) items from a device-side queue, chunk-major */
     int32_t slots;   /* resident CTAs on the device */
     double efficiency; /* modelled useful fraction */
-    int32_t xcut[18];  /* the chunk at position c along x covers owned planes [xcut[c], xcut[c+1]) */
-    int32_t order[16]; /* queue order within a layer: order[i] = position of the i-th chunk. Zig-zag from both
+    int32_t xcut[WAVE3D_MAX_CHUNKS + 2];  /* the chunk at position c along x covers owned planes [xcut[c], xcut[c+1]) */
+    int32_t order[WAVE3D_MAX_CHUNKS]; /* queue order within a layer: order[i] = position of the i-th chunk. Zig-zag from both
                           ends (0, m-1, 1, m-2, ...) keeps x-adjacent chunks — the periodic wrap included —
                           close in the queue; lengths shrink along this order */
 } wave3d_plan;
 
 /* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,nchunks[,s1,s0]" overrides (nchunks 0 = auto). */
 void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan);
+/* style 0: guided chunk lengths (one launch per layer); 1: equal chunks of ~16 planes (multi-layer launch;
+ * env WAVE3D_CHUNK changes the target length). wave3d_plan_make picks the style by box size. */
+void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, wave3d_plan* plan);
 
 /* --- kernel-level entry points (device pointers; stream = cudaStream_t or 0) --- */
 
@@ -218,8 +223,8 @@ typedef struct wave3d_peers {
     double* dst[6];
     int64_t sa[6];
     int64_t sb[6];
-    uint32_t* flag_out[6]; /* neighbour's inbound epoch word for this face pair (NULL: no flag) */
-    uint32_t* flag_in[6];  /* my inbound epoch words (NULL: do not wait) */
+    uint32_t* flag_out[6]; /* neighbour's inbound flag block (WAVE3D_FLAG_WORDS epoch words) for this face pair (NULL: no flag) */
+    uint32_t* flag_in[6];  /* my inbound flag blocks (NULL: do not wait) */
     uint64_t* root_err;    /* rank 0's error table (2*(timesteps+1) u64) or NULL */
 } wave3d_peers;
 
@@ -267,8 +272,9 @@ int wave3d_cuda_field_error(const wave3d_problem* p, const wave3d_box* b, const 
  * until the process exits. `blocks` = number of CTAs (<= 0: the rule of wave3d_cuda_field_error);
  * more than WAVE3D_FIELD_ERROR_STATIC_MAX_BLOCKS is refused with an error. All calls on a device
  * share that array: calls whose kernels may overlap on one GPU must be serialised by the caller.
- * The first call on each device looks up the array's device address (it may load the module), so
- * make it before starting a stream capture on that device. out[0]=max abs, out[1]=max rel. */
+ * Every call looks up the array's device address for the current device (so it stays valid across
+ * cudaDeviceReset); the first call on a device may load the module — make it before starting a
+ * stream capture on that device. out[0]=max abs, out[1]=max rel. */
 #define WAVE3D_FIELD_ERROR_STATIC_MAX_BLOCKS 1184
 int wave3d_cuda_field_error_static(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l,
                                    const double* const tabs[6], const double* u, int n, int blocks, double* out,
@@ -318,6 +324,9 @@ typedef struct wave3d_export {
     wave3d_box box;
     int32_t device;
     int32_t pid;
+    int32_t plan_nchunks;                    /* x-cuts of this rank's tile plan: y/z neighbours with equal cuts */
+    int32_t plan_xcut[WAVE3D_MAX_CHUNKS + 2]; /*   hand-shake per (face, x-chunk) instead of per layer */
+    int32_t reserved;
 } wave3d_export;
 
 int wave3d_solver_export(wave3d_solver* s, int local, wave3d_export* out);
@@ -330,8 +339,10 @@ int wave3d_solver_box(const wave3d_solver* s, int local, wave3d_box* box, wave3d
 double* wave3d_solver_field(wave3d_solver* s, int local, int which);
 void* wave3d_solver_stream(wave3d_solver* s, int local);
 
-/* Phases. reset: zero fields/errors/flags (call before every solve, then barrier
- * across processes). enqueue_*: asynchronous on the rank streams. */
+/* Phases. reset: zero the error table, the flag words and the work-queue / epoch counters (call before
+ * every solve, then barrier across processes). The fields are NOT cleared: layer 0 rewrites every owned
+ * cell and every ghost cell that is read is rewritten by a neighbour (or the wrap) before its first use.
+ * enqueue_*: asynchronous on the rank streams. */
 int wave3d_solver_reset(wave3d_solver* s);
 int wave3d_solver_enqueue_layer0(wave3d_solver* s);
 int wave3d_solver_enqueue_step(wave3d_solver* s, int n);
@@ -372,6 +383,13 @@ int64_t wave3d_solver_kernel_launches(const wave3d_solver* s);
 /* 1 if run()/run_streamed() use the persistent multi-layer launch for layers 2..T (small boxes, one rank per GPU). */
 int wave3d_solver_multistep_active(const wave3d_solver* s);
 int wave3d_solver_status(wave3d_solver* s); /* 0 ok; 1 in-kernel spin timeout on some rank */
+
+/* Debug aids (WAVE3D_DBG_TS=1): per-CTA phase timestamps (8 words per CTA, globaltimer ns) and per-CTA phase
+ * accumulators (16 words per CTA, SM cycles; layout in csrc/wave3d_step_kernel.inc) of the last fused-step
+ * launch on `device` (< 0: the current device). The two arrays (384 KB) stay resident on every GPU that loads
+ * the library. scripts/cta_timeline.py and scripts/cta_phases.py print them. */
+int wave3d_debug_copy_timestamps(unsigned long long* host, int nctas);
+int wave3d_debug_copy_phases(unsigned long long* host, int nctas, int device);
 
 /* The reference program end to end: parse, print "C = ...", solve, write the report. */
 int wave3d_main(int argc, const char* const* argv);

@@ -16,7 +16,7 @@ with open(out, "w") as f:
         ops = collections.Counter()
         lines = []
         for ln in b.splitlines():
-            m = re.match(r"\s+/\*([0-9a-f]{4})\*/\s+(.*?);\s*/\*", ln)
+            m = re.match(r"\s+/\*([0-9a-f]{4,6})\*/\s+(.*?);\s*/\*", ln)
             if m:
                 ins = m.group(2)
                 lines.append(f"/*{m.group(1)}*/  {ins}")

@@ -20,10 +20,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def launch(nproc, args, timeout=300):
+def launch(nproc, args, timeout=300, env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), WORKER] + [str(a) for a in args]
-    env = dict(os.environ, OMP_NUM_THREADS="1")
+    env = dict(os.environ, OMP_NUM_THREADS="1", **(env or {}))
     return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
 
 

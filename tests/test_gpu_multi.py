@@ -39,3 +39,22 @@ def test_one_rank_per_gpu(tmp_path, nproc, dims, transport):
     if transport == "peer":
         assert got["extra"].get("root_table_matches_allreduce") is True
         assert got["streamed_ok"] is True
+
+
+def test_two_processes_share_one_gpu(tmp_path):
+    """More processes than GPUs (the reference's MPS launch mode, ref: cuda_sol.cpp:517-519, README.txt:44-46):
+    the solver must notice, stage the halo through the host over gloo (no kernel waits on another process's
+    flags) and still produce the single-rank maxima bit for bit."""
+    if NGPU < 1:
+        pytest.skip("needs a GPU")
+    out = tmp_path / "res.json"
+    r = launch(2, ["cuda", "auto", 45, 6, "-", out], timeout=600, env={"CUDA_VISIBLE_DEVICES": "0"})
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[:3000] + "\n...\n" + r.stderr[-1500:]
+    got = json.load(open(out))
+    ref = _ref(45, 6)
+    assert got["transport"] == "staged"
+    assert got["abs"] == ref.max_abs and got["rel"] == ref.max_rel
+    assert got["abs2"] == ref.max_abs and got["rel2"] == ref.max_rel
+    # asking for the peer transport in this situation is an error that names the alternatives
+    r = launch(2, ["cuda", "peer", 45, 6, "-", tmp_path / "x.json"], timeout=600, env={"CUDA_VISIBLE_DEVICES": "0"})
+    assert r.returncode != 0 and "one GPU per process" in (r.stdout + r.stderr)
