@@ -161,6 +161,7 @@ def _sig(lib):
         "wave3d_solver_exchange_local": (i32, [vp, i32]),
         "wave3d_solver_sync": (i32, [vp]),
         "wave3d_solver_run": (i32, [vp, C.POINTER(Timings)]),
+        "wave3d_solver_measure_phases": (i32, [vp, C.POINTER(Timings)]),
         "wave3d_solver_run_streamed": (i32, [vp, vp, i32, D, C.POINTER(Timings)]),
         "wave3d_solver_errors": (i32, [vp, D, D]),
         "wave3d_solver_layer_error": (i32, [vp, i32, D]),

@@ -225,6 +225,20 @@ class WaveSolver:
 
     solve = run
 
+    def measure_phases(self) -> SolveResult:
+        """Whole solve plus the reference's phase totals (ref: cuda_sol.cpp:438-441): `extra` carries
+        exchange_ms (peer path: time CTAs waited for a neighbour rank's flag), error_ms (cost of the fused
+        error evaluation, from one extra solve without it), hostdev_ms (0) and loop_ms (the rest)."""
+        t = _lib.Timings()
+        before = self.launches
+        self._chk(_lib.lib().wave3d_solver_measure_phases(self._h, C.byref(t)), "solver_measure_phases")
+        a, r = self.errors()
+        return SolveResult(a, r, t.solve_ms, self.init_ms, self.launches - before, self.nranks, self.dims,
+                           self.problem.cells, self.problem.timesteps,
+                           {"plan": self.plan(0).as_dict() if self.backend == "cuda" else None,
+                            "exchange_ms": t.exchange_ms, "loop_ms": t.loop_ms, "error_ms": t.error_ms,
+                            "hostdev_ms": t.hostdev_ms})
+
     def make_descriptors(self):
         """Pinned host tensor [timesteps+1, 2] with every layer's step inputs (time argument, coefficient)."""
         import torch
@@ -281,6 +295,7 @@ class WaveSolver:
     def report(self, res: SolveResult, precision: int = 0) -> str:
         return _report.format_report(self.problem, res.max_abs, res.max_rel, res.solve_ms, res.init_ms,
                                      loop_ms=res.extra.get("loop_ms"), exchange_ms=res.extra.get("exchange_ms", 0.0),
+                                     error_ms=res.extra.get("error_ms", 0.0),
                                      precision=precision, cuda_style=self.backend == "cuda")
 
     def write_report(self, res: SolveResult, path: Optional[str] = None, precision: int = 0) -> str:

@@ -16,11 +16,11 @@ def output_name(N: int, np_: int, ng: int = 0) -> str:
 
 def format_report(p: Problem, max_abs: Sequence[float], max_rel: Sequence[float], solve_ms: float = 0.0,
                   init_ms: float = 0.0, loop_ms: Optional[float] = None, exchange_ms: float = 0.0,
-                  precision: int = 0, cuda_style: bool = True) -> str:
+                  error_ms: float = 0.0, precision: int = 0, cuda_style: bool = True) -> str:
     n = p.native()
     L = p.timesteps + 1
     assert len(max_abs) == L and len(max_rel) == L
-    t = _lib.Timings(init_ms, solve_ms, solve_ms if loop_ms is None else loop_ms, exchange_ms, 0.0, 0.0)
+    t = _lib.Timings(init_ms, solve_ms, solve_ms if loop_ms is None else loop_ms, exchange_ms, 0.0, error_ms)
     A = (C.c_double * L)(*max_abs)
     R = (C.c_double * L)(*max_rel)
     need = _lib.lib().wave3d_format_report(C.byref(n), C.byref(t), A, R, precision, int(cuda_style), None, 0)

@@ -47,6 +47,7 @@ struct StepLaunch {
                          // per layer and side), zeroed before the solve
     uint32_t* chunkdone; // multi-layer launches: 8 * 4 * WAVE3D_MAX_CHUNKS words (y/z face strips done per x-chunk)
     int yz_chunk_flags;  // y/z neighbours use the same x-cuts: hand-shake per (face, x-chunk)
+    int noerr;           // timing aid: skip the error evaluation
     const double* desc;  // device pointer to {arg_t, coef} or nullptr
     // streamed multi-layer launch: descriptor table in device memory (NaN until uploaded), mapped host
     // memory for the layer maxima and their ready flags

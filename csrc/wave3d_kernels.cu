@@ -453,6 +453,7 @@ int launch_step(const StepLaunch& a) {
     p.stepdone = a.stepdone;
     p.facedone = a.stepdone ? a.stepdone + (pr->timesteps + 2) : nullptr;
     p.chunkdone = a.chunkdone;
+    p.noerr = a.noerr;
     p.yz_chunk_flags = multi && a.chunkdone && a.yz_chunk_flags ? 1 : 0;
     p.desc_tab = multi ? a.desc_tab : nullptr;
     p.host_res = multi ? a.host_res : nullptr;

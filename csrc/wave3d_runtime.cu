@@ -99,6 +99,8 @@ struct wave3d_solver {
     std::vector<cudaEvent_t> sev;  // streamed solve: per layer, per device group
     int xev_used = 0;
     bool fresh = false;  // reset() was called and nothing ran since
+    bool noerr = false;  // timing aid of wave3d_solver_measure_phases: kernels skip the error evaluation
+    bool eager = false;  // ... and launches are not replayed from the CUDA graph (same launch mode for the A/B pair)
 };
 
 namespace {
@@ -298,6 +300,7 @@ void fill_launch(wave3d_solver* s, Rank& r, StepLaunch& a) {
     a.stepdone = r.stepdone;
     a.chunkdone = r.chunkdone;
     a.yz_chunk_flags = r.yz_chunk_flags ? 1 : 0;
+    a.noerr = s->noerr ? 1 : 0;
     a.spin_timeout_s = s->opts.spin_timeout_s;
     a.div_mode = s->div_mode;
     a.stream = stream_of(s, r);
@@ -378,7 +381,7 @@ bool multistep_ok(const wave3d_solver* s) {
 static bool small_box(const wave3d_box* b) { return (double)b->n[0] * b->n[1] * b->n[2] <= 48e6; }
 
 // style 0: guided chunk lengths (one launch per layer: long chunks first, short ones last, so that the
-//          end of every launch is balanced); style 1: equal chunks of ~16 planes (multi-layer launch: no
+//          end of every launch is balanced); style 1: equal chunks of ~32 planes (multi-layer launch: no
 //          per-layer tail to balance, fine items keep the dataflow between layers loose, and every rank
 //          with the same x extent cuts x the same way, which the per-chunk y/z hand-shake needs).
 extern "C" void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, wave3d_plan* plan) {
@@ -392,7 +395,9 @@ extern "C" void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, 
     int ov[5] = {0, 0, 0, 0, 0};
     int nov = 0;
     if (const char* e = getenv("WAVE3D_TILE")) nov = sscanf(e, "%d,%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3], &ov[4]);
-    int chunk_len = 16;
+    // measured at N=256 on one B200: 16 planes 181, 24: ~195, 32: 202, 43: ~198, 64: 175 Gcell/s (longer chunks
+    // amortise the per-item fences and halo planes, too few items per CTA and layer stiffen the dataflow)
+    int chunk_len = 32;
     if (const char* e = getenv("WAVE3D_CHUNK")) chunk_len = std::max(2, atoi(e));
     for (int rj = 1; rj <= 2; rj *= 2) {
         for (int warps = 2; warps <= 7; warps++) {
@@ -1203,7 +1208,7 @@ int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
     }
     const bool per_step = s->opts.per_step_sync != 0;
     // the multi-layer path is a handful of launches: nothing for a graph to save
-    const bool graph = s->opts.use_graph && !per_step && !staged && !multistep_ok(s);
+    const bool graph = s->opts.use_graph && !per_step && !staged && !multistep_ok(s) && !s->noerr && !s->eager;
     if (graph) {
         for (auto& g : s->groups) {
             if (g.exec) continue;
@@ -1259,6 +1264,17 @@ int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, s->xev[2 * i], s->xev[2 * i + 1]) == cudaSuccess) s->exchange_ms += ms;
     }
+    if (!staged && s->connected) {
+        // Fused peer path: the faces travel inside the update kernel; what remains of an "exchange" is the
+        // time CTAs had nothing to load because a neighbour rank's flag had not arrived. Every CTA adds its
+        // share (ns) to scratch words 4-5; reported: mean over the CTAs, max over the local ranks.
+        for (auto& r : s->ranks) {
+            unsigned long long ns = 0;
+            if (use_device(r.device)) return -1;
+            W3D_TRY(cudaMemcpy(&ns, r.scratch + 4, 8, cudaMemcpyDeviceToHost));
+            s->exchange_ms = std::max(s->exchange_ms, (double)ns * 1e-6 / std::max(1, r.plan.ctas));
+        }
+    }
     if (t) {
         t->solve_ms = solve;
         t->exchange_ms = s->exchange_ms;
@@ -1267,6 +1283,33 @@ int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t) {
     if (wave3d_solver_status(s) != 0) {
         set_last_error("in-kernel halo wait timed out (a neighbour rank did not publish its layer)");
         return -2;
+    }
+    return 0;
+}
+
+// The reference reports four phase totals (ref: cuda_sol.cpp:438-441). Here the phases are fused into one
+// kernel, so they are attributed by measurement: the solve runs once with the error evaluation switched off
+// (same launches, same traffic) and once normally; the difference is the cost of the fused error evaluation,
+// the flag waits of the normal run are the exchange time, nothing is staged through the host.
+int wave3d_solver_measure_phases(wave3d_solver* s, wave3d_timings* t) {
+    if (!s || !t) return -1;
+    wave3d_timings t0, t1;
+    if (s->opts.backend == WAVE3D_BACKEND_CUDA) {
+        // the A/B pair uses the same launch mode (eager), the solve that is reported the normal one
+        s->eager = true;
+        s->noerr = true;
+        int rc = wave3d_solver_run(s, &t0);
+        s->noerr = false;
+        if (!rc) rc = wave3d_solver_run(s, &t1);
+        s->eager = false;
+        if (rc) return rc;
+    }
+    int rc = wave3d_solver_run(s, t);
+    if (rc) return rc;
+    if (s->opts.backend == WAVE3D_BACKEND_CUDA) {
+        t->error_ms = std::max(0.0, t1.solve_ms - t0.solve_ms);
+        t->loop_ms = std::max(0.0, t->solve_ms - t->exchange_ms - t->error_ms);
+        t->hostdev_ms = 0.0;  // nothing is staged through the host on either CUDA transport
     }
     return 0;
 }
@@ -1360,7 +1403,15 @@ int wave3d_main(int argc, const char* const* argv) {
             for (int n = 1; n <= p.timesteps; n++) printf("calculating layer %d\n", n);
             fflush(stdout);
         }
-        rc = wave3d_solver_run(s, &tm);
+        // the four phase totals of the reference's report need a second, error-free solve (WAVE3D_PHASES=0
+        // skips it: "total error calculation time" then reads 0)
+        const char* ph = getenv("WAVE3D_PHASES");
+        const bool phases = o.backend == WAVE3D_BACKEND_CUDA && !(ph && !atoi(ph)) && !getenv("WAVE3D_REPEAT");
+        rc = phases ? wave3d_solver_measure_phases(s, &tm) : wave3d_solver_run(s, &tm);
+        // WAVE3D_REPEAT=k: solve k times and report the last one (warm kernels, loaded modules) — for
+        // A/B timing from the command line; the result is the same every time
+        if (const char* e = getenv("WAVE3D_REPEAT"))
+            for (int i = 1; !rc && i < atoi(e); i++) rc = wave3d_solver_run(s, &tm);
     }
     if (rc) {
         fprintf(stderr, "wave3d: solve failed: %s\n", wave3d_cuda_last_error());

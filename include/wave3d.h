@@ -113,10 +113,12 @@ void wave3d_layout_init(const wave3d_box* box, wave3d_layout* lay);
 typedef struct wave3d_timings {
     double init_ms;     /* allocation + tables (ref: "initialization done in") */
     double solve_ms;    /* layer 0 .. layer timesteps incl. errors + halos (ref: cuda_sol.cpp:382,422-425) */
-    double loop_ms;     /* sum of update kernels */
-    double exchange_ms; /* staged halo transport time (0 on the fused peer path) */
-    double hostdev_ms;  /* host<->device staging (0: nothing is staged through the host) */
-    double error_ms;    /* separate error kernels (0: fused) */
+    double loop_ms;     /* update work: solve - exchange - error */
+    double exchange_ms; /* staged transport: time of the exchanges; fused peer path: time CTAs waited for a
+                           neighbour rank's flag (mean over the CTAs, max over the ranks) */
+    double hostdev_ms;  /* host<->device staging: always 0, nothing is staged through the host */
+    double error_ms;    /* cost of the fused error evaluation, measured by wave3d_solver_measure_phases
+                           (0 after a plain run) */
 } wave3d_timings;
 
 /* Render the rank-0 report exactly in the reference's line format
@@ -199,7 +201,7 @@ typedef struct wave3d_plan {
 
 /* Choose the tile plan. sms<=0 -> 148. Env WAVE3D_TILE="ty,rj,nchunks[,s1,s0]" overrides (nchunks 0 = auto). */
 void wave3d_plan_make(const wave3d_box* b, int sms, wave3d_plan* plan);
-/* style 0: guided chunk lengths (one launch per layer); 1: equal chunks of ~16 planes (multi-layer launch;
+/* style 0: guided chunk lengths (one launch per layer); 1: equal chunks of ~32 planes (multi-layer launch;
  * env WAVE3D_CHUNK changes the target length). wave3d_plan_make picks the style by box size. */
 void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, wave3d_plan* plan);
 
@@ -363,6 +365,12 @@ int wave3d_solver_sync(wave3d_solver* s);
  * With nlocal == nranks this is the complete program; with one rank per
  * process call it on every rank between two barriers. */
 int wave3d_solver_run(wave3d_solver* s, wave3d_timings* t);
+
+/* Whole solve plus the reference's four phase totals (ref: cuda_sol.cpp:438-441), attributed by measurement:
+ * one extra solve with the error evaluation switched off gives error_ms (the difference), exchange_ms is the
+ * time CTAs waited for a neighbour rank's flag (peer transport; mean over CTAs, max over ranks) or the staged
+ * exchanges, hostdev_ms is 0 (nothing is staged through the host), loop_ms is the rest. Results as run(). */
+int wave3d_solver_measure_phases(wave3d_solver* s, wave3d_timings* t);
 
 /* Streamed solve = the end-to-end flavour of a whole solve through the per-step API: for every layer the
  * step descriptor (wave3d_step_descriptor) is copied host->device from `pinned_desc` (2 doubles per layer,

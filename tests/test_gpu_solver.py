@@ -166,6 +166,32 @@ def test_staged_transport_reports_exchange_time():
     assert float(line.split()[-2]) > 0.0
 
 
+def test_report_phase_totals_on_the_fused_peer_path(tmp_path):
+    """The reference prints four phase totals (ref: cuda_sol.cpp:438-441). On the fused peer path they are
+    attributed by measurement: exchange = time CTAs waited for a neighbour rank's flag, error = cost of the
+    fused error evaluation (one extra solve without it), host-device = 0 by construction."""
+    p = w.Problem(N=160, T=0.0125, timesteps=10)
+    with w.WaveSolver(p, nranks=2, backend="cuda", devices=[0], transport="peer") as s:
+        plain = s.run()
+        res = s.measure_phases()
+        txt = s.report(res)
+    assert res.max_abs == plain.max_abs and res.max_rel == plain.max_rel  # the timing aid leaves the results alone
+    assert res.extra["exchange_ms"] > 0.0 and res.extra["error_ms"] > 0.0 and res.extra["hostdev_ms"] == 0.0
+    assert 0.0 < res.extra["loop_ms"] < res.solve_ms
+    lines = {l.split(":")[0]: float(l.split()[-2]) for l in txt.splitlines() if l.startswith("total ")}
+    assert lines["total MPI exchange time"] > 0.0 and lines["total error calculation time"] > 0.0
+    assert lines["total host-device exchange time"] == 0.0 and lines["total loop time"] > 0.0
+    # the command-line program does the same by default
+    exe = os.path.join(_lib.REPO, "bin", "wave3d")
+    out = subprocess.run([exe, "160", "2", "1", "1", "1", "0.0125", "10"], cwd=tmp_path, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert [l for l in out.stdout.splitlines() if l.startswith("calculating layer")] == [
+        f"calculating layer {n}" for n in range(1, 11)]  # ref: cuda_sol.cpp:338,385
+    cli = {l.split(":")[0]: float(l.split()[-2]) for l in (tmp_path / "output_N160_Np2.txt").read_text().splitlines()
+           if l.startswith("total ")}
+    assert cli["total error calculation time"] > 0.0 and cli["total MPI exchange time"] > 0.0
+
+
 @pytest.mark.parametrize("lag", [0, 1, 3])
 def test_streamed_solve_equals_batch_solve(lag):
     p = w.Problem(N=56, Lx=1.0, Ly=2.0, Lz=3.0, T=0.05, timesteps=7)
@@ -199,3 +225,29 @@ def test_post_pass_field_error_equals_fused_error():
             assert s.field_error(6) == (res.max_abs[6], res.max_rel[6])
             assert s.field_error(5) == (res.max_abs[5], res.max_rel[5])
             assert s.run().max_abs == res.max_abs  # the scratch borrowed for the post-pass does not disturb a solve
+
+
+def test_planner_model_ranks_candidate_plans_like_the_gpu_does(monkeypatch):
+    """The planner's efficiency model is a handful of calibrated constants; this pins what matters about it:
+    for three candidate tile shapes at N=256 its ranking agrees with measured solve times (plans whose
+    measured times are within 4 % of each other may swap)."""
+    p = w.Problem(N=256, T=0.025, timesteps=20)
+    cands = ["14,2", "10,2", "7,1"]
+    model, meas = [], []
+    for c in cands:
+        monkeypatch.setenv("WAVE3D_TILE", c)
+        with w.WaveSolver(p, backend="cuda") as s:
+            model.append(s.plan(0).efficiency)
+            s.run()
+            meas.append(min(s.run().solve_ms for _ in range(3)))
+    monkeypatch.delenv("WAVE3D_TILE")
+    with w.WaveSolver(p, backend="cuda") as s:
+        chosen = s.plan(0)
+    # the automatic choice is the candidate the model likes best, and it is (one of) the fastest measured
+    best_model = max(range(3), key=lambda i: model[i])
+    assert f"{chosen.ty},{chosen.rj}" == cands[best_model]
+    assert meas[best_model] <= 1.04 * min(meas), (cands, model, meas)
+    for i in range(3):
+        for j in range(3):
+            if model[i] > model[j] and meas[i] > 1.04 * meas[j]:
+                raise AssertionError(f"model prefers {cands[i]} over {cands[j]} but it is slower: {model} {meas}")
