@@ -123,16 +123,26 @@ __global__ void k_tables(TabParams tp, double* sx, double* sy, double* sz, doubl
     else { sz[t] = s; rsz[t] = r; }
 }
 
-__global__ void k_layer0(double* u, const double* sx, const double* sy, const double* sz, double arg_t, int X, int Y,
-                         int Z, int64_t ps, int64_t pitch, int oz) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+// Layer 0 = the analytic solution on every owned cell. Write-only and bandwidth-bound: each thread owns a
+// 16-byte aligned pair of storage columns (one STG.128 per plane where both cells are owned) and walks a strided
+// set of planes with the y/z table values in registers.
+__global__ void __launch_bounds__(256) k_layer0(double* u, const double* sx, const double* sy, const double* sz,
+                                                double arg_t, int X, int Y, int Z, int64_t ps, int64_t pitch, int oz) {
+    const int c0 = 2 * (blockIdx.x * blockDim.x + threadIdx.x);  // storage column of my first cell (even)
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    if (k >= Z || j >= Y) return;
+    const int k0 = c0 - oz, k1 = k0 + 1;                          // owned z indices of the pair
+    const bool v0 = k0 >= 0 && k0 < Z, v1 = k1 >= 0 && k1 < Z;
+    if (j >= Y || !(v0 || v1)) return;
     const double c = cos(arg_t);
-    const double syj = sy[j], szk = sz[k];
+    const double syj = sy[j];
+    const double s0 = v0 ? sz[k0] : 0.0, s1 = v1 ? sz[k1] : 0.0;
+    double* row = u + (int64_t)(j + 1) * pitch + c0;
     for (int i = blockIdx.z; i < X; i += gridDim.z) {
-        const double f = __dmul_rn(__dmul_rn(__dmul_rn(c, sx[i]), syj), szk);
-        u[(int64_t)(i + 1) * ps + (int64_t)(j + 1) * pitch + (oz + k)] = f;
+        const double cxy = __dmul_rn(__dmul_rn(c, sx[i]), syj);
+        double* q = row + (int64_t)(i + 1) * ps;
+        if (v0 && v1) *reinterpret_cast<double2*>(q) = make_double2(__dmul_rn(cxy, s0), __dmul_rn(cxy, s1));
+        else if (v0) q[0] = __dmul_rn(cxy, s0);
+        else q[1] = __dmul_rn(cxy, s1);
     }
 }
 
@@ -202,24 +212,46 @@ struct FErrParams {
     double arg_t;
 };
 __global__ void __launch_bounds__(256) k_field_error(FErrParams g, const double* u, const double* sx, const double* sy,
-                                                      const double* sz, unsigned long long* scratch, double* out) {
+                                                      const double* sz, const double* rsx, const double* rsy,
+                                                      const double* rsz, unsigned long long* scratch, double* out) {
     __shared__ double s_a[8], s_r[8];
     __shared__ bool s_last;
     const double c = cos(g.arg_t);
+    const double rc = __ddiv_rn(1.0, fabs(c));
     const int nk = g.hi[2] - g.lo[2] + 1, nj = g.hi[1] - g.lo[1] + 1, ni = g.hi[0] - g.lo[0] + 1;
     const int64_t rows = (int64_t)ni * nj;
-    double ma = 0.0, mr = 0.0;
+    double ma = 0.0, mr = 0.0, thr = 0.0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // one warp per row, lanes stride along z
+    // One warp per row, lanes stride along z, four cells per lane in flight. max|u-f|/|f| uses the same monotone
+    // filter as the fused kernel: a candidate from the reciprocal tables (~1e-15 relative) and the IEEE division
+    // only for cells within 2^-40 of the thread's best — exactly the maximum of the reference's per-cell division.
     for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
         const int i = g.lo[0] + (int)(row / nj), j = g.lo[1] + (int)(row % nj);
         const double csy = __dmul_rn(__dmul_rn(c, sx[i]), sy[j]);
+        const double rcsy = __dmul_rn(__dmul_rn(rc, rsx[i]), rsy[j]);
         const double* r = u + (int64_t)(i + 1) * g.ps + (int64_t)(j + 1) * g.pitch + g.oz;
-        for (int k = g.lo[2] + lane; k < g.lo[2] + nk; k += 32) {
-            const double f = __dmul_rn(csy, sz[k]);
-            const double a = fabs(__dsub_rn(r[k], f));
-            ma = fmax(ma, a);
-            mr = fmax(mr, __ddiv_rn(a, fabs(f)));
+        for (int k = g.lo[2] + lane; k < g.lo[2] + nk; k += 128) {
+            double v[4], s[4], q[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int kk = k + 32 * t;
+                const bool in = kk < g.lo[2] + nk;
+                v[t] = in ? r[kk] : 0.0;
+                s[t] = in ? sz[kk] : 0.0;
+                q[t] = in ? rsz[kk] : 0.0;
+            }
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                if (k + 32 * t >= g.lo[2] + nk) break;
+                const double f = __dmul_rn(csy, s[t]);
+                const double a = fabs(__dsub_rn(v[t], f));
+                ma = fmax(ma, a);
+                const double cand = __dmul_rn(__dmul_rn(a, rcsy), q[t]);
+                if (cand >= thr) {
+                    mr = fmax(mr, __ddiv_rn(a, fabs(f)));
+                    thr = fmax(thr, __dmul_rn(cand, 1.0 - 0x1p-40));
+                }
+            }
         }
     }
     ma = warp_max(ma);
@@ -558,8 +590,10 @@ int wave3d_cuda_tables(const wave3d_problem* p, const wave3d_box* b, double* sx,
 
 int wave3d_cuda_layer0(const wave3d_problem* p, const wave3d_box* b, const wave3d_layout* l, const double* sx,
                        const double* sy, const double* sz, double* u0, void* stream) {
+    // pairs of storage columns from column (oz & ~1) on; the pitch is a multiple of 16 doubles, so pairs are 16-byte aligned
     dim3 block(64, 4);
-    dim3 grid((b->n[2] + 63) / 64, (b->n[1] + 3) / 4, b->n[0] < 64 ? b->n[0] : 64);
+    const int pairs = (l->oz + b->n[2] + 1) / 2;
+    dim3 grid((pairs + 63) / 64, (b->n[1] + 3) / 4, b->n[0] < 32 ? b->n[0] : 32);
     const double arg_t = std::fma(p->a_t * 0.0, p->tau, p->pi + p->pi);
     k_layer0<<<grid, block, 0, (cudaStream_t)stream>>>(u0, sx, sy, sz, arg_t, b->n[0], b->n[1], b->n[2],
                                                         l->plane_stride, l->pitch, l->oz);
@@ -642,7 +676,7 @@ int wave3d_cuda_field_error(const wave3d_problem* p, const wave3d_box* b, const 
     int64_t blocks = (rows + 7) / 8;
     if (blocks > 1184) blocks = 1184;
     if (blocks < 1) blocks = 1;
-    k_field_error<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(g, u, tabs[0], tabs[1], tabs[2],
+    k_field_error<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(g, u, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], tabs[5],
                                                                  reinterpret_cast<unsigned long long*>(scratch), out);
     W3D_TRY(cudaGetLastError());
     return 0;
@@ -760,7 +794,8 @@ extern "C" int wave3d_cuda_field_error_static(const wave3d_problem* p, const wav
     // the previous call's partial maxima may stay (every CTA overwrites its own slot before the
     // last CTA reads them); the ticket must start at zero
     W3D_TRY(cudaMemsetAsync(scratch, 0, 16, (cudaStream_t)stream));
-    k_field_error<<<(int)nb, 256, 0, (cudaStream_t)stream>>>(g, u, tabs[0], tabs[1], tabs[2], scratch, out);
+    k_field_error<<<(int)nb, 256, 0, (cudaStream_t)stream>>>(g, u, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], tabs[5],
+                                                             scratch, out);
     W3D_TRY(cudaGetLastError());
     return 0;
 }

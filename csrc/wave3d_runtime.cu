@@ -395,10 +395,12 @@ extern "C" void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, 
     int ov[5] = {0, 0, 0, 0, 0};
     int nov = 0;
     if (const char* e = getenv("WAVE3D_TILE")) nov = sscanf(e, "%d,%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3], &ov[4]);
-    // measured at N=256 on one B200: 16 planes 181, 24: ~195, 32: 202, 43: ~198, 64: 175 Gcell/s (longer chunks
-    // amortise the per-item fences and halo planes, too few items per CTA and layer stiffen the dataflow)
-    int chunk_len = 32;
-    if (const char* e = getenv("WAVE3D_CHUNK")) chunk_len = std::max(2, atoi(e));
+    // Chunk length of the multi-layer style: long chunks amortise the per-item fences and the two halo planes,
+    // but a CTA should still get 2-3 items per layer or the dataflow between layers stiffens. Measured: 76 tiles
+    // (256^3 box): 16 planes 181, 24: ~195, 32: 202, 43: ~198, 64: 175 Gcell/s; 152 tiles (257x257x513 box on 4
+    // GPUs): 32: 838, 43: 878, 64: 871 Gcell/s. Rule: ~2.5 items per CTA and layer, never shorter than 32 planes.
+    int chunk_env = 0;
+    if (const char* e = getenv("WAVE3D_CHUNK")) chunk_env = std::max(2, atoi(e));
     for (int rj = 1; rj <= 2; rj *= 2) {
         for (int warps = 2; warps <= 7; warps++) {
             const int ty = rj * warps;
@@ -448,7 +450,14 @@ extern "C" void wave3d_plan_make_style(const wave3d_box* b, int sms, int style, 
                 for (int c = 1; c <= m; c++) cuts[c] = (int)((int64_t)X * c / m);
                 for (int i = 0; i < m; i++) ord[i] = (i % 2 == 0) ? i / 2 : m - 1 - i / 2;
             } else if (style) {
+                int chunk_len = chunk_env;
+                if (!chunk_len) {
+                    const int want = std::max(1, (int)std::lround(2.5 * slots / ntiles));
+                    chunk_len = std::max(32, X / want);
+                }
                 m = std::max(1, std::min(mmax, (X + chunk_len / 2) / chunk_len));
+                // tiny boxes: rather short chunks than idle CTAs
+                while (!chunk_env && ntiles * m < slots && m < mmax && X / (m + 1) >= 8) m++;
                 for (int c = 1; c <= m; c++) cuts[c] = (int)((int64_t)X * c / m);
                 for (int i = 0; i < m; i++) ord[i] = (i % 2 == 0) ? i / 2 : m - 1 - i / 2;
             } else {
