@@ -426,10 +426,10 @@ int launch_step(const StepLaunch& a) {
         set_last_error("plan.rj must be 1 or 2");
         return -1;
     }
-    if (pl->warps < 1 || pl->warps > kMaxWarps || pl->ty != pl->rj * pl->warps || pl->tz != 64 || pl->s1 < 4 ||
+    if (pl->warps < 1 || pl->warps > kMaxWarps || pl->ty != pl->rj * pl->warps || pl->tz != 64 || pl->s1 < 4 || pl->s1 > 16 ||
         pl->s0 < 1 || pl->ctas < 1 || pl->nchunks < 1 || pl->nchunks > kMaxChunks || pl->xcut[0] != 0 ||
         pl->xcut[pl->nchunks] != b->n[0]) {
-        set_last_error("invalid tile plan (s1 >= 4, s0 >= 1, nchunks <= WAVE3D_MAX_CHUNKS)");
+        set_last_error("invalid tile plan (4 <= s1 <= 16, s0 >= 1, nchunks <= WAVE3D_MAX_CHUNKS)");
         return -1;
     }
     {
