@@ -1,29 +1,30 @@
 // wave3d_kernels.cu — sm_100a device code of the wave3d solver.
 //
-// Hot kernel: k_step<RJ,FIRST,DIV> — one launch per time layer that fuses what the
-// reference spreads over K2/K3 (update), K4 (boundary planes), K5/K6 + 12 memcpys +
-// MPI p2p (halo exchange), K7 + host loop (error max) and two memsets
-// (ref: cuda_sol.cpp:384-421, cuda_sol_kernels.cu:24-268).
+// Hot kernel: k_step<RJ,FIRST,DIV,MULTI> (wave3d_step_kernel.inc) — one launch per time layer, or one
+// persistent launch for all layers of a small box, that fuses what the reference spreads over K2/K3
+// (update), K4 (boundary planes), K5/K6 + 12 memcpys + MPI p2p (halo exchange), K7 + host loop (error max)
+// and two memsets (ref: cuda_sol.cpp:384-421, cuda_sol_kernels.cu:24-268).
 //
 // Design (B200-first, not a translation):
-//   * The stencil source layer u^{n-1} and the in-place layer u^{n-2} stream through
-//     shared memory as y-z tiles, one x plane at a time, moved by TMA bulk tensor
-//     loads (cp.async.bulk.tensor.3d -> UTMALDG) into mbarrier-guarded rings; threads
-//     never issue a global load on the hot path.
-//   * Each thread owns 2 z-cells x RJ rows, reads its 7-point neighbourhood from the
-//     three resident planes and writes u^n with one 16-byte store over u^{n-2}.
-//   * The analytic solution is separable: f = ((c*sx[i])*sy[j])*sz[k] with 1-D sine
-//     tables -> bit-identical to the reference's per-cell trig at 3 multiplies.
-//     max|u-f| is an in-register max; max|u-f|/|f| uses a monotone filter so the
-//     exact IEEE division runs only for candidates of the maximum.
-//   * Face cells are stored a second time, straight into the neighbour GPU's ghost
-//     cells (peer-mapped memory over NVLink; own memory for the periodic self-wrap).
-//     The last CTA of the grid publishes an epoch flag per neighbour with
-//     st.release.sys; the next step's CTAs ld.acquire.sys-spin on their inbound flags.
+//   * The stencil source layer u^{n-1} and the in-place layer u^{n-2} stream through shared memory as
+//     y-z tiles, one x plane at a time, moved by TMA bulk tensor loads (cp.async.bulk.tensor.3d ->
+//     UTMALDG) into mbarrier-guarded rings by a scheduler warp that works one item ahead; the compute
+//     warps never issue a global or constant-bank load on the hot path (tables, layer constants and
+//     tile geometry reach them through shared memory).
+//   * Each thread owns 2 z-cells x RJ rows, reads its 7-point neighbourhood from the three resident
+//     planes and writes u^n with one 16-byte store over u^{n-2}.
+//   * The analytic solution is separable: f = ((c*sx[i])*sy[j])*sz[k] with 1-D sine tables ->
+//     bit-identical to the reference's per-cell trig at 3 multiplies. max|u-f| is an in-register max;
+//     max|u-f|/|f| uses a monotone filter with a CTA-shared threshold so the exact IEEE division runs
+//     only for candidates of the maximum.
+//   * Face cells are stored a second time, straight into the neighbour GPU's ghost cells (peer-mapped
+//     memory over NVLink; own memory for the periodic self-wrap). Epoch flags in the receiver's memory
+//     (per face, and per x-chunk for y/z faces in the multi-layer launch) are the handshake: published
+//     with one system-scope fence by whoever completes a layer / strip, polled by the scheduler warps.
 //     No pack/unpack kernels, no host staging, no MPI/NCCL on this path.
-//   * Per-layer maxima land in err[2n..2n+1] via atomicMax on the u64 bit pattern
-//     (values are >= 0; NaN never wins, like fmax) and are forwarded to rank 0's
-//     table with a system-scope atomic (the reference's deferred MPI_Reduce).
+//   * Per-layer maxima land in err[2n..2n+1] via atomicMax on the u64 bit pattern (values are >= 0; NaN
+//     never wins, like fmax) and are forwarded to rank 0's table with a system-scope atomic (the
+//     reference's deferred MPI_Reduce).
 #include "wave3d_internal.hpp"
 
 #include <cmath>
@@ -541,7 +542,7 @@ int launch_step(const StepLaunch& a) {
     const int smem = plan_smem_bytes(pl->ty, pl->tz, pl->s1, a.first ? 0 : pl->s0);
     if (ensure_smem_attr((const void*)k, smem)) return -1;
     const int grid = pl->ctas;  // persistent CTAs pulling (tile, x-chunk) items from the device-side queue
-    const int block = (pl->warps + 1) * 32;  // + the TMA producer warp
+    const int block = (pl->warps + 1) * 32;  // + the scheduler warp (TMA loads, queue, dependencies, flags)
     if (multi) {
         // items wait on each other inside the kernel: every CTA must be resident
         void* args[1] = {&p};
