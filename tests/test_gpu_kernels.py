@@ -167,3 +167,39 @@ def test_fused_rel_error_filter_equals_exact_division():
     a, r = K.step(p, box, lay, tabs, u0, u1, 1, True)
     fa, fr = K.field_error(p, box, lay, tabs, u1, 1)
     assert (a, r) == (fa, fr)
+
+
+def test_step_rejects_plans_whose_end_chunks_miss_the_seam_planes():
+    """The x-face flags (and the periodic wrap inside one box) are released when the chunks at the two ends of a
+    tile column are done, so those chunks have to contain the seam planes send_x[0] / send_x[1]; cuts must
+    increase strictly and the ring depths are bounded. A caller-supplied plan that breaks this is refused."""
+    p = w.Problem(N=40, T=0.05, timesteps=4)
+    dec = Decomposition.create(p.N, 1)
+    box, lay = dec.box(0), dec.layout(0)
+    tabs = K.tables(p, box, DEV)
+    u0, u1 = K.alloc_field(lay, DEV), K.alloc_field(lay, DEV)
+    K.layer0(p, box, lay, tabs, u0)
+    good = K.plan_for(box)
+    K.step(p, box, lay, tabs, u0, u1, 1, first=True, plan=good)  # the planner's own plan is fine
+
+    def broken(edit):
+        pl = _lib.Plan.from_buffer_copy(bytes(good))
+        edit(pl)
+        with pytest.raises(RuntimeError, match="tile plan"):
+            K.step(p, box, lay, tabs, u0, u1, 1, first=True, plan=pl)
+
+    def one_plane_end_chunk(pl):
+        pl.nchunks = 3
+        pl.xcut[0], pl.xcut[1], pl.xcut[2], pl.xcut[3] = 0, 1, 20, box.n[0]   # seam plane 1 is not in chunk 0
+        pl.order[0], pl.order[1], pl.order[2] = 0, 2, 1
+    broken(one_plane_end_chunk)
+
+    def not_increasing(pl):
+        pl.nchunks = 3
+        pl.xcut[0], pl.xcut[1], pl.xcut[2], pl.xcut[3] = 0, 20, 20, box.n[0]
+        pl.order[0], pl.order[1], pl.order[2] = 0, 2, 1
+    broken(not_increasing)
+
+    def ring_too_deep(pl):
+        pl.s1 = 17
+    broken(ring_too_deep)
