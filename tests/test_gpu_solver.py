@@ -62,6 +62,24 @@ def test_decomposition_invariance_peer_transport(nranks, dims):
     assert res.max_rel == ref.max_rel
 
 
+@pytest.mark.parametrize("nranks,dims", [(2, (1, 1, 2)), (2, (1, 2, 1)), (8, (2, 2, 2))])
+@pytest.mark.parametrize("sched", ["0", "8"])
+def test_full_tiles_on_rank_faces_keep_the_maxima(nranks, dims, sched, monkeypatch):
+    """N=128 gives every rank 64-column tiles that are full (but for, at most, the 64th column: a wall or a
+    neighbour's ghost column) AND lie on a y/z rank face: they take the march variant that is the
+    predicate-free one plus the ghost stores (WAVE3D_SCHED=8 sends them through the general variant instead).
+    Either way the maxima are those of the undivided box, bit for bit."""
+    p = w.Problem(N=128, Lx=1.0, Ly=2.0, Lz=_lib.PI_FULL, T=0.025, timesteps=8)
+    with w.WaveSolver(p, nranks=1, backend="cuda") as s:
+        ref = s.run()
+    monkeypatch.setenv("WAVE3D_SCHED", sched)
+    with w.WaveSolver(p, nranks=nranks, dims=dims, backend="cuda", devices=[0]) as s:
+        res = s.run()
+        assert s.status() == 0
+    assert res.max_abs == ref.max_abs
+    assert res.max_rel == ref.max_rel
+
+
 @pytest.mark.parametrize("nranks,dims", [(2, None), (8, None), (4, (1, 4, 1))])
 def test_staged_transport_equals_peer(nranks, dims):
     p = w.Problem(N=40, T=0.05, timesteps=6)
